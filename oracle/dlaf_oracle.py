@@ -1,0 +1,441 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY (not the product; never imported by the product package).
+
+CPU restatement (numpy + scipy LAPACK/BLAS for tile arithmetic) of the reference Cholesky path of
+DLA-Future v0.6.0. The reference itself cannot be built here; parity is pinned on
+the reference's own analytical known-answer tests, which `tests/test_oracle.py` replays against
+this file. Citations are relative to /root/reference.
+
+  Distribution index algebra   include/dlaf/matrix/util_distribution.h:27-200, distribution.h
+  analytical setters           test/include/dlaf_test/matrix/util_generic_lapack.h:27-68
+  local call_L / call_U        include/dlaf/factorization/cholesky/impl.h:150-189, :316-348
+  distributed call_L / call_U  include/dlaf/factorization/cholesky/impl.h:191-313, :350-452
+  panel broadcast routing      include/dlaf/communication/broadcast_panel.h:59-213
+  residual                     miniapp/miniapp_cholesky.cpp:408-442
+"""
+import ctypes
+import glob
+import os
+import subprocess
+
+import numpy as np
+import scipy.linalg.blas as sblas
+import scipy.linalg.lapack as slapack
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+DTYPES = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
+
+
+def type_error(dtype):
+    """TypeUtilities<T>::error: 2*eps real, 8*eps complex (test/include/dlaf_test/util_types.h:40,:62)."""
+    dtype = np.dtype(dtype)
+    eps = np.finfo(dtype).eps
+    return (8 if dtype.kind == "c" else 2) * float(eps)
+
+
+# ----------------------------------------------------------------------------------------------
+# Distribution (2D block-cyclic index algebra), one tile per block, no element offset.
+# ----------------------------------------------------------------------------------------------
+class Distribution:
+    """matrix::Distribution restricted to what the Cholesky path uses.
+
+    rank_global_tile: util_distribution.h:85-95; local_tile_from_global_tile: :110-125;
+    next_local_tile_from_global_tile: :150-175; local_nr_tiles via next_local(nr_tiles).
+    """
+
+    def __init__(self, n, nb, grid=(1, 1), rank=(0, 0), src=(0, 0)):
+        self.n, self.nb = int(n), int(nb)
+        self.grid, self.rank, self.src = tuple(grid), tuple(rank), tuple(src)
+        self.nt = -(-self.n // self.nb) if self.n > 0 else 0
+
+    def rank_global_tile(self, g, axis):
+        return (g + self.src[axis]) % self.grid[axis]
+
+    def local_tile_from_global(self, g, axis):
+        return g // self.grid[axis]
+
+    def next_local_tile_from_global(self, g, axis, rank=None):
+        r = self.rank[axis] if rank is None else rank
+        P = self.grid[axis]
+        rank_to_src = (r + P - self.src[axis]) % P
+        owner_to_src = g % P  # == (rank_global_tile + P - src) % P
+        local = g // P
+        return local + 1 if rank_to_src < owner_to_src else local
+
+    def local_nr_tiles(self, axis, rank=None):
+        return self.next_local_tile_from_global(self.nt, axis, rank)
+
+    def global_tile_from_local(self, l, axis, rank=None):
+        r = self.rank[axis] if rank is None else rank
+        P = self.grid[axis]
+        return l * P + (r + P - self.src[axis]) % P
+
+    def tile_size(self, g):
+        return min(self.nb, self.n - g * self.nb)
+
+    def local_size(self, axis, rank=None):
+        return sum(self.tile_size(self.global_tile_from_local(l, axis, rank))
+                   for l in range(self.local_nr_tiles(axis, rank)))
+
+
+# ----------------------------------------------------------------------------------------------
+# Analytical known-answer pair (getCholeskySetters).
+# ----------------------------------------------------------------------------------------------
+def cholesky_setters(n, uplo, dtype, rows=None, cols=None):
+    """Returns (A, T) restricted to global index arrays rows x cols (default: full n x n).
+
+    t_ij = 2^-|i-j| e^{I(j-i)},  a_ij = (4^(min(i,j)+1)-1)/(3*2^(i+j)) e^{I(j-i)}; the triangle
+    that is not referenced holds -9.9 (util_generic_lapack.h:40-68).
+    """
+    dtype = np.dtype(dtype)
+    rows = np.arange(n) if rows is None else np.asarray(rows)
+    cols = np.arange(n) if cols is None else np.asarray(cols)
+    i = rows[:, None].astype(np.float64)
+    j = cols[None, :].astype(np.float64)
+    mag_a = np.exp2(-(i + j)) / 3 * (np.exp2(2 * (np.minimum(i, j) + 1)) - 1)
+    mag_t = np.exp2(-np.abs(i - j))
+    if dtype.kind == "c":
+        ph = np.exp(1j * (j - i))
+        a, t = mag_a * ph, mag_t * ph
+    else:
+        a, t = mag_a + 0 * j, mag_t + 0 * j
+    unref = (i < j) if uplo == "L" else (i > j)
+    a = np.where(unref, -9.9, a)
+    t = np.where(unref, -9.9, t)
+    return np.asfortranarray(a.astype(dtype)), np.asfortranarray(t.astype(dtype))
+
+
+def check_near(actual, expected, abs_tol, rel_tol=None):
+    """CHECK_MATRIX_NEAR: passes if abs diff <= abs_tol OR rel diff <= rel_tol
+    (test/include/dlaf_test/matrix/util_matrix.h:255-283). Returns the number of failing entries."""
+    rel_tol = abs_tol if rel_tol is None else rel_tol
+    diff = np.abs(actual - expected)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        rel = diff / np.abs(expected)
+    ok = (diff <= abs_tol) | (rel <= rel_tol)
+    return int(np.count_nonzero(~ok))
+
+
+# ----------------------------------------------------------------------------------------------
+# Tile kernels (what the reference MC backend calls through lapackpp / blaspp).
+# ----------------------------------------------------------------------------------------------
+def _f(name, dtype):
+    pre = {np.float32: "s", np.float64: "d", np.complex64: "c", np.complex128: "z"}[np.dtype(dtype).type]
+    mod = slapack if name == "potrf" else sblas
+    if name == "herk" and pre in "sd":
+        name = "syrk"
+    return getattr(mod, pre + name)
+
+
+def tile_potrf(uplo, a):
+    """lapack/tile.h:363-378. Returns info; a is overwritten in the uplo triangle only."""
+    if a.shape[0] == 0:
+        return 0
+    c, info = _f("potrf", a.dtype)(a, lower=(uplo == "L"), clean=False, overwrite_a=False)
+    tri = np.tril if uplo == "L" else np.triu
+    mask = tri(np.ones(a.shape, dtype=bool))
+    if info == 0:
+        a[mask] = c[mask]
+    return info
+
+
+def tile_trsm_L(lkk, b):
+    """b <- b * lkk^-H (Right, Lower, ConjTrans, NonUnit, alpha=1), impl.h:55-67."""
+    if b.size:
+        b[...] = _f("trsm", b.dtype)(1.0, lkk, b, side=1, lower=1, trans_a=2, diag=0)
+
+
+def tile_trsm_U(ukk, b):
+    """b <- ukk^-H * b (Left, Upper, ConjTrans, NonUnit, alpha=1), impl.h:107-119."""
+    if b.size:
+        b[...] = _f("trsm", b.dtype)(1.0, ukk, b, side=0, lower=0, trans_a=2, diag=0)
+
+
+def tile_herk_L(a, c):
+    """c <- c - a a^H on the lower triangle (impl.h:69-80)."""
+    if c.size and a.size:
+        r = _f("herk", c.dtype)(-1.0, a, beta=1.0, c=c, trans=0, lower=1)
+        m = np.tril(np.ones(c.shape, dtype=bool))
+        c[m] = r[m]
+
+
+def tile_herk_U(a, c):
+    """c <- c - a^H a on the upper triangle (impl.h:121-132)."""
+    if c.size and a.size:
+        tr = 2 if np.dtype(c.dtype).kind == "c" else 1
+        r = _f("herk", c.dtype)(-1.0, a, beta=1.0, c=c, trans=tr, lower=0)
+        m = np.triu(np.ones(c.shape, dtype=bool))
+        c[m] = r[m]
+
+
+def tile_gemm_L(a, b, c):
+    """c <- c - a b^H (impl.h:82-94)."""
+    if c.size and a.size:
+        c[...] = _f("gemm", c.dtype)(-1.0, a, b, beta=1.0, c=c, trans_a=0, trans_b=2)
+
+
+def tile_gemm_U(a, b, c):
+    """c <- c - a^H b (impl.h:134-146)."""
+    if c.size and a.size:
+        c[...] = _f("gemm", c.dtype)(-1.0, a, b, beta=1.0, c=c, trans_a=2, trans_b=0)
+
+
+# ----------------------------------------------------------------------------------------------
+# Local tiled algorithm (impl.h:150-189, :316-348).
+# ----------------------------------------------------------------------------------------------
+def cholesky_local(uplo, a, nb):
+    """In-place tiled right-looking Cholesky of the column-major array `a` (n x n). Returns info
+    (0, or k*nb + tile info of the first failing diagonal tile: ScaLAPACK-style global column)."""
+    n = a.shape[0]
+    nt = -(-n // nb) if n else 0
+    t = lambda i, j: a[i * nb:min(n, (i + 1) * nb), j * nb:min(n, (j + 1) * nb)]
+    for k in range(nt):
+        info = tile_potrf(uplo, t(k, k))
+        if info:
+            return k * nb + info
+        for i in range(k + 1, nt):
+            if uplo == "L":
+                tile_trsm_L(t(k, k), t(i, k))
+            else:
+                tile_trsm_U(t(k, k), t(k, i))
+        for j in range(k + 1, nt):
+            if uplo == "L":
+                tile_herk_L(t(j, k), t(j, j))
+                for i in range(j + 1, nt):
+                    tile_gemm_L(t(i, k), t(j, k), t(i, j))
+            else:
+                tile_herk_U(t(k, j), t(j, j))
+                for i in range(j + 1, nt):
+                    tile_gemm_U(t(k, j), t(k, i), t(j, i))
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------
+# Distributed algorithm with simulated ranks (impl.h:191-313, :350-452; broadcast_panel.h).
+# ----------------------------------------------------------------------------------------------
+def scatter(a_global, nb, grid, src=(0, 0)):
+    """Global matrix -> {rank: dict[(gi,gj)] -> tile copy} following rank_global_tile."""
+    n = a_global.shape[0]
+    d0 = Distribution(n, nb, grid, (0, 0), src)
+    local = {(r, c): {} for r in range(grid[0]) for c in range(grid[1])}
+    for gi in range(d0.nt):
+        for gj in range(d0.nt):
+            owner = (d0.rank_global_tile(gi, 0), d0.rank_global_tile(gj, 1))
+            local[owner][(gi, gj)] = np.array(
+                a_global[gi * nb:min(n, (gi + 1) * nb), gj * nb:min(n, (gj + 1) * nb)], order="F")
+    return local
+
+
+def gather(local, n, nb, dtype):
+    out = np.zeros((n, n), dtype=dtype, order="F")
+    for tiles in local.values():
+        for (gi, gj), t in tiles.items():
+            out[gi * nb:gi * nb + t.shape[0], gj * nb:gj * nb + t.shape[1]] = t
+    return out
+
+
+def panel_broadcast_plan(dist, k, axis="col"):
+    """Tile routing of one step of `broadcast(root, panel, panelT, row_chain, col_chain)`
+    (broadcast_panel.h:123-213) for the column panel k of a Lower factorization (axis='col') or
+    the row panel k of an Upper factorization (axis='row'), seen from rank `dist.rank`.
+
+    Returns (step1, step2):
+      step1: list of (global_tile_index_along_panel, root_rank_in_orthogonal_axis) this rank holds
+             in `panel` after the first broadcast (root = rank owning grid column/row of k);
+      step2: list of (global_tile_index, root_rank_along_panel_axis) for every slot of `panelT`
+             this rank fills; the LAST global tile is not transposed (:186-191) unless this rank
+             does not own it.
+    """
+    kt = k + 1
+    ax_p = 0 if axis == "col" else 1      # axis along which panel tiles are indexed
+    ax_t = 1 - ax_p                       # axis along which panelT tiles are indexed
+    root1 = dist.rank_global_tile(k, ax_t)
+    step1 = []
+    for l in range(dist.next_local_tile_from_global(kt, ax_p), dist.local_nr_tiles(ax_p)):
+        step1.append((dist.global_tile_from_local(l, ax_p), root1))
+    step2 = []
+    last = max(kt, dist.nt - 1)
+    lo = dist.next_local_tile_from_global(kt, ax_t)
+    hi = dist.local_nr_tiles(ax_t)
+    if dist.rank[ax_t] == dist.rank_global_tile(last, ax_t):
+        hi -= 1
+    for l in range(lo, hi):
+        g = dist.global_tile_from_local(l, ax_t)
+        step2.append((g, dist.rank_global_tile(g, ax_p)))
+    return step1, step2
+
+
+def cholesky_distributed(uplo, local, n, nb, grid, src=(0, 0)):
+    """Runs call_L / call_U over simulated ranks. `local` is the output of scatter() and is
+    updated in place. Each rank only ever touches its own tiles plus what a broadcast delivers;
+    the asserts check the routing tables of panel_broadcast_plan against tile ownership."""
+    P, Q = grid
+    ranks = [(r, c) for r in range(P) for c in range(Q)]
+    dists = {rc: Distribution(n, nb, grid, rc, src) for rc in ranks}
+    d0 = dists[(0, 0)]
+    nt = d0.nt
+    lower = uplo == "L"
+    for k in range(nt):
+        kk_rank = (d0.rank_global_tile(k, 0), d0.rank_global_tile(k, 1))
+        info = tile_potrf(uplo, local[kk_rank][(k, k)])
+        if info:
+            return k * nb + info
+        kt = k + 1
+        if kt == nt:
+            continue
+        lkk = local[kk_rank][(k, k)]
+        # diagonal tile broadcast along the column (L) / row (U) communicator, then panel update
+        for rc in ranks:
+            if lower and rc[1] == kk_rank[1]:
+                for (gi, gj), t in local[rc].items():
+                    if gj == k and gi > k:
+                        tile_trsm_L(lkk, t)
+            if not lower and rc[0] == kk_rank[0]:
+                for (gi, gj), t in local[rc].items():
+                    if gi == k and gj > k:
+                        tile_trsm_U(lkk, t)
+        # panel / panelT broadcast (routing per broadcast_panel.h)
+        panels, panelsT = {}, {}
+        for rc in ranks:
+            d = dists[rc]
+            step1, step2 = panel_broadcast_plan(d, k, "col" if lower else "row")
+            pan, panT = {}, {}
+            for g, root in step1:
+                owner = (rc[0], root) if lower else (root, rc[1])
+                key = (g, k) if lower else (k, g)
+                assert key in local[owner], (rc, key, owner)
+                pan[g] = local[owner][key]
+            for g, root in step2:
+                # the tile comes from the rank (in my column / row) that holds it in ITS panel
+                holder = (root, rc[1]) if lower else (rc[0], root)
+                s1, _ = panel_broadcast_plan(dists[holder], k, "col" if lower else "row")
+                assert g in [x for x, _ in s1], (rc, g, holder)
+                src_owner = (holder[0], s1[0][1]) if lower else (s1[0][1], holder[1])
+                key = (g, k) if lower else (k, g)
+                panT[g] = local[src_owner][key]
+            panels[rc], panelsT[rc] = pan, panT
+        # trailing matrix
+        for rc in ranks:
+            pan, panT = panels[rc], panelsT[rc]
+            for (gi, gj), t in local[rc].items():
+                if lower and gj >= kt and gi >= gj:
+                    if gi == gj:
+                        tile_herk_L(pan[gi], t)
+                    else:
+                        tile_gemm_L(pan[gi], panT[gj], t)
+                if not lower and gi >= kt and gj >= gi:
+                    if gi == gj:
+                        tile_herk_U(pan[gj], t)
+                    else:
+                        tile_gemm_U(panT[gi], pan[gj], t)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------
+# Residuals.
+# ----------------------------------------------------------------------------------------------
+def residual_max(a, l, uplo="L"):
+    """max|A - L L^H| / max|A| over the referenced triangle (miniapp_cholesky.cpp:408-442).
+    Returns (ratio, eps*n) so that callers can apply the miniapp thresholds."""
+    n = a.shape[0]
+    if n == 0:
+        return 0.0, 0.0
+    if uplo == "L":
+        f = np.tril(l)
+        d = np.tril(a - f @ f.conj().T)
+        na = np.abs(np.tril(a)).max()
+    else:
+        f = np.triu(l)
+        d = np.triu(a - f.conj().T @ f)
+        na = np.abs(np.triu(a)).max()
+    return float(np.abs(d).max() / na), float(np.finfo(a.dtype).eps * n)
+
+
+def residual_inf(a_herm, l, uplo="L"):
+    """north_star form: ||A - L L^H||_inf / (||A||_inf * n * eps), A given as full Hermitian."""
+    n = a_herm.shape[0]
+    f = np.tril(l) if uplo == "L" else np.triu(l).conj().T
+    d = a_herm - f @ f.conj().T
+    return float(np.abs(d).sum(axis=1).max() /
+                 (np.abs(a_herm).sum(axis=1).max() * n * np.finfo(a_herm.dtype).eps))
+
+
+def residual_probe(a_full_herm_matvec, l, x):
+    """Size-independent check for big n: || A x - L (L^H x) || / (||A x||) with O(n^2) work.
+    `a_full_herm_matvec(x)` returns A @ x."""
+    f = np.tril(l)
+    ax = a_full_herm_matvec(x)
+    r = ax - f @ (f.conj().T @ x)
+    return float(np.linalg.norm(r) / np.linalg.norm(ax))
+
+
+# ----------------------------------------------------------------------------------------------
+# C++ oracle (threaded tile tasks + exact mt19937_64 generator): build + ctypes binding.
+# ----------------------------------------------------------------------------------------------
+_LIB = None
+
+
+def blas_path():
+    import scipy
+    c = sorted(glob.glob(os.path.join(os.path.dirname(os.path.dirname(scipy.__file__)), "scipy.libs",
+                                      "libscipy_openblas*.so")))
+    if not c:
+        raise RuntimeError("scipy-bundled OpenBLAS not found")
+    return c[0]
+
+
+def build(force=False):
+    so = os.path.join(HERE, "_build", "liboracle.so")
+    src = os.path.join(HERE, "chol_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        os.makedirs(os.path.dirname(so), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-fopenmp", "-shared", "-fPIC", "-o", so, src, "-ldl"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(HERE, "_build", "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        L = ctypes.CDLL(so)
+        if L.oracle_set_blas(blas_path().encode(), 1) != 0:
+            raise RuntimeError("oracle: cannot dlopen OpenBLAS")
+        i64, vp = ctypes.c_int64, ctypes.c_void_p
+        for x in "sdcz":
+            getattr(L, f"oracle_gen_hpd_{x}").argtypes = [i64, i64, vp, i64]
+            getattr(L, f"oracle_gen_hpd_{x}").restype = None
+            getattr(L, f"oracle_cholesky_local_{x}").argtypes = [ctypes.c_char, i64, i64, vp, i64]
+            getattr(L, f"oracle_residual_lower_{x}").argtypes = [i64, vp, i64, vp, i64,
+                                                                 ctypes.POINTER(ctypes.c_double)]
+            getattr(L, f"oracle_residual_lower_{x}").restype = ctypes.c_double
+        L.oracle_lapack_potrf_d.argtypes = [ctypes.c_char, i64, vp, i64]
+        L.oracle_set_threads.argtypes = [ctypes.c_int, ctypes.c_int]
+        L.oracle_set_threads.restype = None
+        _LIB = L
+    return _LIB
+
+
+def _x(dtype):
+    return {np.float32: "s", np.float64: "d", np.complex64: "c", np.complex128: "z"}[np.dtype(dtype).type]
+
+
+def gen_hpd(n, nb, dtype):
+    """set_random_hermitian_positive_definite on a 1x1 grid: full Hermitian n x n, column-major."""
+    a = np.zeros((n, n), dtype=dtype, order="F")
+    if n:
+        getattr(lib(), f"oracle_gen_hpd_{_x(dtype)}")(n, nb, a.ctypes.data, a.strides[1] // a.itemsize)
+    return a
+
+
+def cholesky_local_threaded(uplo, a, nb, task_threads=None, blas_threads=1):
+    """C++ tile-task Cholesky (one single-threaded BLAS call per tile task) — the CPU baseline."""
+    L = lib()
+    if task_threads is None:
+        task_threads = os.cpu_count() or 1
+    L.oracle_set_threads(task_threads, blas_threads)
+    assert a.flags.f_contiguous
+    n = a.shape[0]
+    return getattr(L, f"oracle_cholesky_local_{_x(a.dtype)}")(uplo.encode(), n, nb, a.ctypes.data,
+                                                              max(1, a.strides[1] // a.itemsize))
