@@ -1,0 +1,45 @@
+# Builds the product library (CUDA kernels + C++ host layer + C API) in-tree for sm_100a.
+#   make            -> dla-future_b200/lib/libdlaf_b200.so
+#   make miniapp    -> dla-future_b200/bin/miniapp_cholesky
+#   make oracle     -> oracle/_build/liboracle.so (test infrastructure only)
+NVCC      ?= /usr/local/cuda/bin/nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+PKG       := dla-future_b200
+CSRC      := $(PKG)/csrc
+SRC       := $(PKG)/src
+BUILD     := build
+LIBDIR    := $(PKG)/lib
+BINDIR    := $(PKG)/bin
+NVFLAGS   := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-Wall,-Wno-unused-function -Iinclude -I$(CSRC) -I$(SRC)
+
+CU_SRCS   := $(wildcard $(CSRC)/*.cu) $(wildcard $(SRC)/*.cu)
+OBJS      := $(patsubst %.cu,$(BUILD)/%.o,$(notdir $(CU_SRCS)))
+HDRS      := $(wildcard $(CSRC)/*.cuh) $(wildcard $(SRC)/*.h) $(wildcard include/*.h) $(wildcard include/*/*.h) \
+             $(wildcard include/*/*/*.h) $(wildcard include/*/*/*/*.h)
+
+vpath %.cu $(CSRC) $(SRC)
+
+all: $(LIBDIR)/libdlaf_b200.so
+
+$(BUILD)/%.o: %.cu $(HDRS)
+	@mkdir -p $(BUILD)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(LIBDIR)/libdlaf_b200.so: $(OBJS)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart -lnccl
+
+miniapp: $(BINDIR)/miniapp_cholesky
+
+$(BINDIR)/miniapp_cholesky: miniapp/miniapp_cholesky.cpp $(LIBDIR)/libdlaf_b200.so $(HDRS)
+	@mkdir -p $(BINDIR)
+	$(NVCC) $(ARCH) -O2 -std=c++17 -Iinclude -o $@ $< -L$(LIBDIR) -ldlaf_b200 -Xlinker -rpath -Xlinker '$$ORIGIN/../lib' -lcudart
+
+oracle:
+	@mkdir -p oracle/_build
+	g++ -O2 -fopenmp -shared -fPIC -o oracle/_build/liboracle.so oracle/chol_oracle.cpp -ldl
+
+clean:
+	rm -rf $(BUILD) $(LIBDIR) $(BINDIR)
+
+.PHONY: all miniapp oracle clean

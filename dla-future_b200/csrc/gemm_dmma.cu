@@ -1,0 +1,272 @@
+// TMA + DMMA FP64 contraction kernel (see gemm_dmma.cuh). sm_100a only.
+#include "gemm_dmma.cuh"
+
+#include <cstdio>
+
+namespace dlafb {
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+    gemm_nt_dmma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                        const GemmParams p) {
+  // ---- which block of C ----
+  int trow, tcol, row0, col0, lower, m_lim = p.m_total, n_lim = p.n_total;
+  if (p.list != nullptr) {
+    const int nsub = p.sub * p.sub;
+    const int item = blockIdx.x / nsub;
+    const int s = blockIdx.x - item * nsub;
+    const int2 it = p.list[item];
+    lower = it.y < 0;
+    trow = (s % p.sub) * kBM;
+    tcol = (s / p.sub) * kBN;
+    row0 = it.x + trow;
+    col0 = (it.y & 0x7fffffff) + tcol;
+    m_lim = min(m_lim, it.x + p.tile);
+    n_lim = min(n_lim, (it.y & 0x7fffffff) + p.tile);
+  }
+  else {
+    lower = p.lower;
+    trow = blockIdx.x * kBM;
+    tcol = blockIdx.y * kBN;
+    row0 = p.rect_row0 + trow;
+    col0 = p.rect_col0 + tcol;
+  }
+  if (row0 >= m_lim || col0 >= n_lim)
+    return;
+  if (lower && trow + kBM - 1 < tcol)
+    return;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_full = base + kStages * kStageBytes;
+  const uint32_t bar_empty = bar_full + 8 * kStages;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 8);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  const int nk = p.K / kBK;
+
+  if (warp == 8) {
+    // ---- TMA producer: one lane feeds the ring of stages ----
+    if (lane == 0) {
+      const int a_row = row0 + p.a_row_off;
+      const int b_row = col0 + p.b_row_off;
+      for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % kStages;
+        const uint32_t ph = (kt / kStages) & 1;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t full = bar_full + 8 * s;
+        mbar_expect_tx(full, kStageBytes);
+        const uint32_t sa = base + s * kStageBytes;
+        const uint32_t sb = sa + kOperandStageBytes;
+        const int ka = p.a_col0 + kt * kBK;
+        const int kb = p.b_col0 + kt * kBK;
+        if (p.nbox_a == 1)
+          tma_load_3d(sa, &map_a, 0, ka, a_row >> 4, full);
+        else
+          for (int g = 0; g < 8; ++g)
+            tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
+        if (p.nbox_b == 1)
+          tma_load_3d(sb, &map_b, 0, kb, b_row >> 4, full);
+        else
+          for (int g = 0; g < 8; ++g)
+            tma_load_2d(sb + g * kGroupBytes, &map_b, b_row + 16 * g, kb, full);
+      }
+    }
+    return;
+  }
+
+  // ---- DMMA consumers: 8 warps as 2 (rows) x 4 (cols); each owns a 64 x 32 block of C ----
+  const int wm = warp & 1;
+  const int wn = warp >> 1;
+  const int r = lane >> 2;   // fragment row (A) / column (B)
+  const int kk = lane & 3;   // fragment k index; MMA step s4 uses k-columns 8*(s4/2) + 2*kk + (s4&1)
+
+  double acc[8][4][2];
+#pragma unroll
+  for (int f = 0; f < 8; ++f)
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+      acc[f][g][0] = acc[f][g][1] = 0.0;
+
+  // Swizzle<3,4,3> of the 128B rows: 16-byte chunk index ^= (k-column & 7). With the k permutation above
+  // the 16 lanes of a half-warp hit 16 distinct 8-byte bank pairs.
+  uint32_t xo[2][2];
+#pragma unroll
+  for (int fb = 0; fb < 2; ++fb)
+#pragma unroll
+    for (int sb = 0; sb < 2; ++sb)
+      xo[fb][sb] = (((uint32_t)((fb << 2) | (r >> 1)) ^ (uint32_t)((kk << 1) | sb)) << 4) + ((r & 1) << 3);
+  const uint32_t a_thr = (wm * 4) * kGroupBytes + (2 * kk) * 128;
+  const uint32_t b_thr = kOperandStageBytes + (wn * 2) * kGroupBytes + (2 * kk) * 128;
+
+  for (int kt = 0; kt < nk; ++kt) {
+    const int s = kt % kStages;
+    const uint32_t ph = (kt / kStages) & 1;
+    mbar_wait(bar_full + 8 * s, ph);
+    const uint32_t st = base + s * kStageBytes;
+#pragma unroll
+    for (int s4 = 0; s4 < 4; ++s4) {
+      const uint32_t koff = (8 * (s4 >> 1) + (s4 & 1)) * 128;
+      double a[8], b[4];
+#pragma unroll
+      for (int f = 0; f < 8; ++f)
+        a[f] = lds_f64(st + a_thr + (f >> 1) * kGroupBytes + koff + xo[f & 1][s4 & 1]);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        b[g] = lds_f64(st + b_thr + (g >> 1) * kGroupBytes + koff + xo[g & 1][s4 & 1]);
+#pragma unroll
+      for (int f = 0; f < 8; ++f)
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          dmma884(acc[f][g][0], acc[f][g][1], a[f], b[g]);
+    }
+    __syncwarp();
+    if (lane == 0)
+      mbar_arrive(bar_empty + 8 * s);
+  }
+
+  // ---- epilogue: C <- beta*C + alpha*acc, clipped and (optionally) restricted to the lower triangle ----
+  const double alpha = p.alpha, beta = p.beta;
+  const bool full_block = !lower || (trow >= tcol + kBN - 1);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int cl = wn * 32 + g * 8 + 2 * kk + e;  // column inside the CTA block
+      const int c = col0 + cl;
+      if (c >= n_lim)
+        continue;
+      double* colp = p.C + (long long)c * p.ldc;
+#pragma unroll
+      for (int f = 0; f < 8; ++f) {
+        const int rl = wm * 64 + f * 8 + r;
+        const int rr = row0 + rl;
+        if (rr >= m_lim)
+          continue;
+        if (!full_block && (trow + rl < tcol + cl))
+          continue;
+        double v = alpha * acc[f][g][e];
+        if (beta != 0.0)
+          v = fma(beta, colp[rr], v);
+        colp[rr] = v;
+      }
+    }
+  }
+}
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+}  // namespace
+
+int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
+                     int kind) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc)
+    return -1;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld & 1) || rows <= 0 || cols <= 0)
+    return -2;
+  CUresult r;
+  if (kind == 3) {
+    cuuint64_t dims[3] = {16, (cuuint64_t)cols, (cuuint64_t)((rows + 15) / 16)};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 8, 128};
+    cuuint32_t box[3] = {16, (cuuint32_t)kBK, 8};
+    cuuint32_t es[3] = {1, 1, 1};
+    r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  else {
+    cuuint64_t dims[2] = {(cuuint64_t)rows, (cuuint64_t)cols};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
+    cuuint32_t box[2] = {16, (cuuint32_t)kBK};
+    cuuint32_t es[2] = {1, 1};
+    r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(base), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
+                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y) {
+  static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 kGemmSmemBytes);
+  if (attr != cudaSuccess)
+    return attr;
+  if (nblocks_x == 0 || nblocks_y == 0)
+    return cudaSuccess;
+  gemm_nt_dmma_kernel<<<dim3(nblocks_x, nblocks_y), kGemmThreads, kGemmSmemBytes, stream>>>(map_a, map_b, p);
+  return cudaGetLastError();
+}
+
+}  // namespace dlafb

@@ -1,0 +1,56 @@
+// FP64 contraction kernel of the Cholesky path: C <- beta*C + alpha * A * B^T on 128x128 blocks of C.
+// This is the kernel that replaces the reference's per-tile cublasDgemm / cublasDsyrk / cublasDtrsm calls
+// (include/dlaf/blas/tile.h:370-382, :414-425, :458-470) for the trailing update, the panel solve
+// (multiplication by inverted diagonal blocks) and the blocked diagonal-tile factorization.
+//
+// Data path: TMA (cp.async.bulk.tensor) -> 128B-swizzled shared memory -> DMMA m8n8k4 (mma.sync f64).
+// A and B are column-major panels (rows x K); one pipeline stage holds K-slices of 16 columns of a
+// 128-row block of each, laid out as 8 row-groups of [16 k-columns][16 rows] (128 B per k-column).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dlafb {
+
+constexpr int kBM = 128;      // rows of C per CTA
+constexpr int kBN = 128;      // cols of C per CTA
+constexpr int kBK = 16;       // K-slice per pipeline stage
+constexpr int kStages = 4;    // TMA pipeline depth
+constexpr int kGroupBytes = kBK * 128;             // one 16-row group of one K-slice
+constexpr int kOperandStageBytes = kBM * kBK * 8;  // 16 KiB
+constexpr int kStageBytes = 2 * kOperandStageBytes;
+constexpr int kGemmSmemBytes = kStages * kStageBytes + 2 * kStages * 8 + 1024;  // + barriers + align slack
+constexpr int kGemmThreads = 288;  // 8 DMMA warps + 1 TMA warp
+
+struct GemmParams {
+  double* C;
+  long long ldc;
+  int m_total, n_total;  // C is clipped to [0, m_total) x [0, n_total)
+  int K;                 // contraction length, multiple of kBK
+  int a_col0, b_col0;    // first K column inside the A / B tensor maps
+  int a_row_off, b_row_off;  // A row = C row + a_row_off, B row = C col + b_row_off
+  double alpha, beta;
+  // LIST mode (list != nullptr): one entry per nb x nb tile, x = first row, y = first col | diag<<31;
+  // each tile is covered by sub*sub CTAs.
+  const int2* list;
+  int sub;
+  int tile;  // nb: list tiles are clipped to tile x tile
+  // RECT mode: blocks (blockIdx.x, blockIdx.y) of the rectangle at (rect_row0, rect_col0);
+  // lower != 0 keeps only elements on or below the rectangle's own diagonal.
+  int rect_row0, rect_col0;
+  int lower;
+  int nbox_a, nbox_b;  // 1: 3-D map (one TMA per operand slice), 8: 2-D map (one TMA per 16-row group)
+};
+
+// Builds the tensor map of a column-major FP64 matrix for the layout above. kind 3: rank-3 view
+// (16 rows, cols, row-groups) so that a whole 128 x 16 slice arrives with ONE bulk copy; kind 2: plain
+// rank-2 view with 16 x 16 boxes. Returns 0 on success.
+int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
+                     int kind);
+
+// Launches the kernel for `nblocks_x` x `nblocks_y` CTAs on `stream`.
+cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
+                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y);
+
+}  // namespace dlafb
