@@ -43,13 +43,9 @@ PLAIN_API = {
 
 def declared_symbols():
     """Every symbol the public headers declare (checked by the CPU test-suite against the built library)."""
-    names = [k.format(x=x) for k in TILE_API for x in TYPES] + list(PLAIN_API)
-    try:
-        from . import _engine_api  # noqa: F401
-        names += _engine_api.symbols()
-    except ImportError:
-        pass
-    return names
+    from . import _c_api, _engine_api
+    return ([k.format(x=x) for k in TILE_API for x in TYPES] + list(PLAIN_API) + _engine_api.symbols() +
+            _c_api.symbols())
 
 
 def lib():
@@ -65,13 +61,15 @@ def lib():
         for k, (res, args) in PLAIN_API.items():
             f = getattr(L, k)
             f.restype, f.argtypes = res, args
-        try:
-            from . import _engine_api
-            _engine_api.bind(L)
-        except ImportError:
-            pass
+        from . import _c_api, _engine_api
+        _engine_api.bind(L)
+        _c_api.bind(L)
         _LIB = L
     return _LIB
+
+
+from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
+from ._engine_api import CholeskyPlan, Grid, StepInfo, schedule_step  # noqa: E402,F401
 
 
 def check(err, what=""):

@@ -5,6 +5,9 @@
 #include "tile_ops.cuh"
 
 namespace dlafb {
+
+std::atomic<unsigned long long> g_launches{0};
+
 namespace {
 
 template <class T>
@@ -135,6 +138,19 @@ __global__ void __launch_bounds__(256) max_abs_kernel(int tri, int m, int n, con
   }
 }
 
+template <class T>
+__global__ void __launch_bounds__(256) pack_tiles_kernel(int m, int n, const T* __restrict__ src, long long ld,
+                                                         T* __restrict__ dst, int tile) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= m)
+    return;
+  T* d = dst + (long long)(i / tile) * tile * tile + i % tile;
+  const int j0 = blockIdx.y * 64;
+  const int j1 = min(n, j0 + 64);
+  for (int j = j0; j < j1; ++j)
+    d[(long long)j * tile] = src[i + (long long)j * ld];
+}
+
 inline int tri_code(char c) {
   return (c == 'L' || c == 'l') ? 1 : ((c == 'U' || c == 'u') ? 2 : 0);
 }
@@ -148,6 +164,7 @@ cudaError_t transpose(cudaStream_t stream, int m, int n, const T* in, long long 
     return cudaSuccess;
   transpose_kernel<T><<<dim3(ceil_div(m, 32), ceil_div(n, 32)), 256, 0, stream>>>(m, n, in, ldin, out, ldout, conj,
                                                                                  tri_code(tri));
+  ++g_launches;
   return cudaGetLastError();
 }
 
@@ -157,6 +174,7 @@ cudaError_t laset(cudaStream_t stream, char uplo, int m, int n, T alpha, T beta,
     return cudaSuccess;
   laset_kernel<T><<<dim3(ceil_div(m, 256), ceil_div(n, 64)), 256, 0, stream>>>(tri_code(uplo), m, n, alpha, beta, a,
                                                                               lda);
+  ++g_launches;
   return cudaGetLastError();
 }
 
@@ -165,6 +183,7 @@ cudaError_t lacpy(cudaStream_t stream, char uplo, int m, int n, const T* a, long
   if (m <= 0 || n <= 0)
     return cudaSuccess;
   lacpy_kernel<T><<<dim3(ceil_div(m, 256), ceil_div(n, 64)), 256, 0, stream>>>(tri_code(uplo), m, n, a, lda, b, ldb);
+  ++g_launches;
   return cudaGetLastError();
 }
 
@@ -175,6 +194,7 @@ cudaError_t gen_hpd(cudaStream_t stream, long long n, int nb, int rows, int cols
     return cudaSuccess;
   gen_hpd_kernel<T><<<dim3(ceil_div(rows, 256), ceil_div(cols, 64)), 256, 0, stream>>>(
       n, nb, rows, cols, row_first, row_stride, col_first, col_stride, a, lda, seed);
+  ++g_launches;
   return cudaGetLastError();
 }
 
@@ -183,6 +203,16 @@ cudaError_t max_abs(cudaStream_t stream, char uplo, int m, int n, const T* a, lo
   if (m <= 0 || n <= 0)
     return cudaSuccess;
   max_abs_kernel<T><<<dim3(ceil_div(m, 256), ceil_div(n, 64)), 256, 0, stream>>>(tri_code(uplo), m, n, a, lda, out);
+  ++g_launches;
+  return cudaGetLastError();
+}
+
+template <class T>
+cudaError_t pack_tiles(cudaStream_t stream, int m, int n, const T* src, long long ld, T* dst, int tile) {
+  if (m <= 0 || n <= 0)
+    return cudaSuccess;
+  pack_tiles_kernel<T><<<dim3(ceil_div(m, 256), ceil_div(n, 64)), 256, 0, stream>>>(m, n, src, ld, dst, tile);
+  ++g_launches;
   return cudaGetLastError();
 }
 
@@ -192,7 +222,8 @@ cudaError_t max_abs(cudaStream_t stream, char uplo, int m, int n, const T* a, lo
   template cudaError_t lacpy<T>(cudaStream_t, char, int, int, const T*, long long, T*, long long);                 \
   template cudaError_t gen_hpd<T>(cudaStream_t, long long, int, int, int, int, int, int, int, T*, long long,       \
                                   unsigned long long);                                                             \
-  template cudaError_t max_abs<T>(cudaStream_t, char, int, int, const T*, long long, double*);
+  template cudaError_t max_abs<T>(cudaStream_t, char, int, int, const T*, long long, double*);                      \
+  template cudaError_t pack_tiles<T>(cudaStream_t, int, int, const T*, long long, T*, int);
 DLAFB_INST_AUX(float)
 DLAFB_INST_AUX(double)
 DLAFB_INST_AUX(float2)

@@ -5,7 +5,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace dlafb {
+
+// Number of kernels this library has launched (reported by bench.py as gpu_launches).
+extern std::atomic<unsigned long long> g_launches;
 
 template <class T>
 struct Tr;

@@ -1,6 +1,8 @@
 // TMA + DMMA FP64 contraction kernel (see gemm_dmma.cuh). sm_100a only.
 #include "gemm_dmma.cuh"
 
+#include "common.cuh"
+
 #include <cstdio>
 
 namespace dlafb {
@@ -35,6 +37,13 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
@@ -57,6 +66,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
                         const GemmParams p) {
   // ---- which block of C ----
   int trow, tcol, row0, col0, lower, m_lim = p.m_total, n_lim = p.n_total;
+  int b_from_a = 0, b_row_a = 0;  // LIST mode, diagonal tile: both operands come from the row panel (HERK)
   if (p.list != nullptr) {
     const int nsub = p.sub * p.sub;
     const int item = blockIdx.x / nsub;
@@ -67,6 +77,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     tcol = (s / p.sub) * kBN;
     row0 = it.x + trow;
     col0 = (it.y & 0x7fffffff) + tcol;
+    b_from_a = lower;
+    b_row_a = it.x + tcol + p.a_row_off;
     m_lim = min(m_lim, it.x + p.tile);
     n_lim = min(n_lim, (it.y & 0x7fffffff) + p.tile);
   }
@@ -105,7 +117,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     // ---- TMA producer: one lane feeds the ring of stages ----
     if (lane == 0) {
       const int a_row = row0 + p.a_row_off;
-      const int b_row = col0 + p.b_row_off;
+      const int b_row = b_from_a ? b_row_a : col0 + p.b_row_off;
+      const CUtensorMap* mb = b_from_a ? &map_a : &map_b;
+      const int nbox_b = b_from_a ? p.nbox_a : p.nbox_b;
+      const int b_col0 = b_from_a ? p.a_col0 : p.b_col0;
       for (int kt = 0; kt < nk; ++kt) {
         const int s = kt % kStages;
         const uint32_t ph = (kt / kStages) & 1;
@@ -115,17 +130,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
         const uint32_t sa = base + s * kStageBytes;
         const uint32_t sb = sa + kOperandStageBytes;
         const int ka = p.a_col0 + kt * kBK;
-        const int kb = p.b_col0 + kt * kBK;
+        const int kb = b_col0 + kt * kBK;
         if (p.nbox_a == 1)
           tma_load_3d(sa, &map_a, 0, ka, a_row >> 4, full);
+        else if (p.nbox_a == 4)
+          tma_load_4d(sa, &map_a, 0, ka, (a_row % p.tile) >> 4, a_row / p.tile, full);
         else
           for (int g = 0; g < 8; ++g)
             tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
-        if (p.nbox_b == 1)
-          tma_load_3d(sb, &map_b, 0, kb, b_row >> 4, full);
+        if (nbox_b == 1)
+          tma_load_3d(sb, mb, 0, kb, b_row >> 4, full);
+        else if (nbox_b == 4)
+          tma_load_4d(sb, mb, 0, kb, (b_row % p.tile) >> 4, b_row / p.tile, full);
         else
           for (int g = 0; g < 8; ++g)
-            tma_load_2d(sb + g * kGroupBytes, &map_b, b_row + 16 * g, kb, full);
+            tma_load_2d(sb + g * kGroupBytes, mb, b_row + 16 * g, kb, full);
       }
     }
     return;
@@ -245,6 +264,17 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   }
+  else if (kind == 4) {
+    // tile layout (contiguous ld x ld tiles, ld = tile size): rows = number of tiles * ld, cols = ld
+    const cuuint64_t nb = (cuuint64_t)ld;
+    cuuint64_t dims[4] = {16, nb, nb / 16, (cuuint64_t)(rows / ld)};
+    cuuint64_t strides[3] = {nb * 8, 128, nb * nb * 8};
+    cuuint32_t box[4] = {16, (cuuint32_t)kBK, 8, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<double*>(base), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   else {
     cuuint64_t dims[2] = {(cuuint64_t)rows, (cuuint64_t)cols};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
@@ -266,6 +296,7 @@ cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, c
   if (nblocks_x == 0 || nblocks_y == 0)
     return cudaSuccess;
   gemm_nt_dmma_kernel<<<dim3(nblocks_x, nblocks_y), kGemmThreads, kGemmSmemBytes, stream>>>(map_a, map_b, p);
+  ++g_launches;
   return cudaGetLastError();
 }
 

@@ -40,12 +40,15 @@ struct GemmParams {
   // lower != 0 keeps only elements on or below the rectangle's own diagonal.
   int rect_row0, rect_col0;
   int lower;
-  int nbox_a, nbox_b;  // 1: 3-D map (one TMA per operand slice), 8: 2-D map (one TMA per 16-row group)
+  // 1: rank-3 map (one TMA per operand slice), 8: rank-2 map (one TMA per 16-row group),
+  // 4: rank-4 map of a panel stored as contiguous tile x tile tiles (one TMA per slice)
+  int nbox_a, nbox_b;
 };
 
 // Builds the tensor map of a column-major FP64 matrix for the layout above. kind 3: rank-3 view
 // (16 rows, cols, row-groups) so that a whole 128 x 16 slice arrives with ONE bulk copy; kind 2: plain
-// rank-2 view with 16 x 16 boxes. Returns 0 on success.
+// rank-2 view with 16 x 16 boxes; kind 4: panel in tile layout (rows = ntiles*ld, ld = tile size, cols = ld).
+// Returns 0 on success.
 int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
                      int kind);
 

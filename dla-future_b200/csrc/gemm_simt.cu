@@ -10,6 +10,8 @@ template <class T>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const SimtParams<T> p) {
   using R = typename Tr<T>::Real;
   int trow, tcol, row0, col0, lower, m_lim = p.m_total, n_lim = p.n_total;
+  bool b_from_a = false;
+  int b_row_a = 0;
   if (p.list != nullptr) {
     const int nsub = p.sub * p.sub;
     const int item = blockIdx.x / nsub;
@@ -21,6 +23,8 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const SimtParams<T> p) {
     tcol = (s / p.sub) * kSimtTile;
     row0 = it.x + trow;
     col0 = c0 + tcol;
+    b_from_a = lower;  // diagonal tile of the list: HERK, both operands from the row panel
+    b_row_a = it.x + tcol + p.a_row_off;
     m_lim = min(m_lim, it.x + p.tile);
     n_lim = min(n_lim, c0 + p.tile);
   }
@@ -53,15 +57,19 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const SimtParams<T> p) {
 
   const bool a_ok = row0 + lr < m_lim;
   const bool b_ok = col0 + lr < n_lim;
-  const T* ap = p.A + (row0 + lr + p.a_row_off);
-  const T* bp = p.B + (col0 + lr + p.b_row_off);
+  auto operand = [&](const T* base, int row, int tiled) {
+    return tiled ? base + (long long)(row / p.tile) * p.tile * p.tile + row % p.tile : base + row;
+  };
+  const T* ap = operand(p.A, row0 + lr + p.a_row_off, p.a_tiled);
+  const T* bp = b_from_a ? operand(p.A, b_row_a + lr, p.a_tiled) : operand(p.B, col0 + lr + p.b_row_off, p.b_tiled);
+  const long long ldb = b_from_a ? p.lda : p.ldb;
 
   for (int k0 = 0; k0 < p.K; k0 += kSK) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int k = k0 + lk + 4 * h;
       As[lk + 4 * h][lr] = (a_ok && k < p.K) ? ap[(long long)k * p.lda] : Tr<T>::zero();
-      Bs[lk + 4 * h][lr] = (b_ok && k < p.K) ? bp[(long long)k * p.ldb] : Tr<T>::zero();
+      Bs[lk + 4 * h][lr] = (b_ok && k < p.K) ? bp[(long long)k * ldb] : Tr<T>::zero();
     }
     __syncthreads();
 #pragma unroll
@@ -115,6 +123,7 @@ cudaError_t launch_gemm_simt(cudaStream_t stream, const SimtParams<T>& p, unsign
   if (nblocks_x == 0 || nblocks_y == 0)
     return cudaSuccess;
   gemm_simt_kernel<T><<<dim3(nblocks_x, nblocks_y), 256, 0, stream>>>(p);
+  ++g_launches;
   return cudaGetLastError();
 }
 

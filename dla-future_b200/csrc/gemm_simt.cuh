@@ -28,6 +28,7 @@ struct SimtParams {
   int tile;  // nb: tiles of the list are clipped to tile x tile
   int rect_row0, rect_col0;
   int lower;
+  int a_tiled, b_tiled;  // operand stored as contiguous tile x tile tiles (lda / ldb = tile)
 };
 
 template <class T>

@@ -257,6 +257,7 @@ cudaError_t launch_potf2(cudaStream_t stream, char uplo, int n, T* a, long long 
     return attr;
   kern<<<1, kPotf2Threads, potf2_smem_bytes<T>(n), stream>>>(uplo == 'U' || uplo == 'u', n, a, lda, winv, ldw, info,
                                                              info_base, mode);
+  ++g_launches;
   return cudaGetLastError();
 }
 

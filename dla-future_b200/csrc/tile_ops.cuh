@@ -73,6 +73,11 @@ template <class T>
 cudaError_t gen_hpd(cudaStream_t stream, long long n, int nb, int rows, int cols, int row_first, int row_stride,
                     int col_first, int col_stride, T* a, long long lda, unsigned long long seed);
 
+// Copies the m x n column-major block src into tile layout: row i goes to slot i / tile (contiguous tile x tile
+// column-major tiles) of dst; dst points at the slot of row 0.
+template <class T>
+cudaError_t pack_tiles(cudaStream_t stream, int m, int n, const T* src, long long ld, T* dst, int tile);
+
 // max |a_ij| over the uplo part, atomically combined into *out (double, must be zeroed by the caller).
 template <class T>
 cudaError_t max_abs(cudaStream_t stream, char uplo, int m, int n, const T* a, long long lda, double* out);

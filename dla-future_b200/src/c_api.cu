@@ -1,0 +1,322 @@
+// C API of the Cholesky path: dlaf_initialize / dlaf_finalize, the grid registry, descriptor conversion and the
+// dlaf_cholesky_factorization_{s,d,c,z} / dlaf_p{s,d,c,z}potrf entry points.
+// Reference: src/c_api/init.cpp:21-64, src/c_api/grid.cpp:26-92, src/c_api/utils.cpp:25-69,
+// src/c_api/factorization/cholesky.h:32-77, src/c_api/factorization/cholesky.cpp:16-56.
+// As in the reference the caller's host block is mirrored to the device, factorized there and copied back
+// (matrix::MatrixMirror, include/dlaf/matrix/matrix_mirror.h:110-177); device pointers are used in place.
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <tuple>
+#include <unordered_map>
+
+#include "../../include/dlafb_engine.h"
+#include "../../include/dlafb_mpi_shim/mpi.h"
+#include "grid.h"
+
+#include <dlaf_c/factorization/cholesky.h>
+#include <dlaf_c/init.h>
+// dlaf_c/grid.h includes <mpi.h>; the shim above already defined MPI_Comm
+DLAF_EXTERN_C int dlaf_create_grid(MPI_Comm comm, int nprow, int npcol, char order) DLAF_NOEXCEPT;
+DLAF_EXTERN_C void dlaf_free_grid(int context) DLAF_NOEXCEPT;
+DLAF_EXTERN_C char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow, int mypcol) DLAF_NOEXCEPT;
+DLAF_EXTERN_C void dlaf_create_grid_from_blacs_info(int blacs_ctxt, MPI_Comm comm, int nprow, int npcol,
+                                                    char order) DLAF_NOEXCEPT;
+
+struct dlafb_mpi_comm {
+  int rank = 0, size = 1;
+  ncclComm_t world = nullptr;
+};
+
+namespace {
+
+bool g_initialized = false;
+dlafb_mpi_comm* g_world = nullptr;
+std::unordered_map<int, dlafb_grid_t> g_grids;
+
+struct PlanKey {
+  int ctx;
+  char type, uplo;
+  int n, nb, isrc, jsrc;
+  bool operator<(const PlanKey& o) const {
+    return std::tie(ctx, type, uplo, n, nb, isrc, jsrc) < std::tie(o.ctx, o.type, o.uplo, o.n, o.nb, o.isrc, o.jsrc);
+  }
+};
+struct PlanEntry {
+  dlafb_chol_plan_t plan = nullptr;
+  void* dev = nullptr;  // device mirror of the local block
+  size_t dev_bytes = 0;
+  int64_t ldd = 0;
+  cudaStream_t stream = nullptr;
+};
+std::map<PlanKey, PlanEntry> g_plans;
+
+[[noreturn]] void die(const char* what, int code) {
+  std::fprintf(stderr, "[dlaf_b200] fatal: %s (error %d)\n", what, code);
+  std::abort();  // the reference's DLAF_ASSERT / *_CHECK_ERROR convention: print and terminate
+}
+
+void drop_plans_of(int ctx) {
+  for (auto it = g_plans.begin(); it != g_plans.end();) {
+    if (ctx == INT_MIN || it->first.ctx == ctx) {
+      dlafb_cholesky_plan_destroy(it->second.plan);
+      cudaFree(it->second.dev);
+      if (it->second.stream)
+        cudaStreamDestroy(it->second.stream);
+      it = g_plans.erase(it);
+    }
+    else
+      ++it;
+  }
+}
+
+size_t elem_size(char t) { return t == 's' ? 4 : (t == 'z' ? 16 : 8); }
+
+int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
+  if (!g_initialized)
+    die("dlaf_cholesky_factorization called before dlaf_initialize", -1);
+  if (d.i != 0 || d.j != 0)
+    die("sub-matrix offsets are not supported (desc.i, desc.j must be 0)", -1);  // cholesky.h:37-38
+  if (d.m != d.n || d.mb != d.nb)
+    die("cholesky_factorization needs a square matrix with square blocks", -1);  // factorization/cholesky.h:69-70
+  auto git = g_grids.find(ctx);
+  if (git == g_grids.end())
+    die("no grid registered for this context", ctx);  // utils.cpp:55-69 terminates as well
+  dlafb_grid_t grid = git->second;
+  const PlanKey key{ctx, type, uplo == 'u' ? 'U' : (uplo == 'l' ? 'L' : uplo), d.n, d.nb, d.isrc, d.jsrc};
+  if (key.uplo != 'L' && key.uplo != 'U')
+    die("uplo must be 'L' or 'U'", -1);
+  PlanEntry& pe = g_plans[key];
+  int e;
+  if (!pe.plan) {
+    if ((e = dlafb_cholesky_plan_create(&pe.plan, grid, type, key.uplo, d.n, d.nb, d.isrc, d.jsrc)) != 0)
+      die("plan creation failed", e);
+    if (cudaStreamCreateWithFlags(&pe.stream, cudaStreamNonBlocking) != cudaSuccess)
+      die("stream creation failed", -1);
+  }
+  int64_t rows = 0, cols = 0;
+  dlafb_cholesky_plan_local_size(pe.plan, &rows, &cols);
+  if (rows > 0 && d.ld < rows)
+    die("leading dimension smaller than the local number of rows", d.ld);
+  const size_t es = elem_size(type);
+  cudaPointerAttributes attr{};
+  const bool on_device = (a != nullptr) && cudaPointerGetAttributes(&attr, a) == cudaSuccess &&
+                         (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+  cudaGetLastError();
+  int info = 0;
+  if (on_device) {
+    if ((e = dlafb_cholesky_plan_run(pe.plan, a, d.ld, pe.stream)) != 0)
+      die("factorization failed to launch", e);
+  }
+  else {
+    const int64_t ldd = ((rows > 0 ? rows : 1) + 63) / 64 * 64;  // default device layout: matrix.h:87-89
+    const size_t need = (size_t)ldd * (size_t)(cols > 0 ? cols : 1) * es + 1024;
+    if (pe.dev_bytes < need) {
+      cudaFree(pe.dev);
+      if (cudaMalloc(&pe.dev, need) != cudaSuccess)
+        die("device allocation of the mirror failed", -1);
+      pe.dev_bytes = need;
+    }
+    pe.ldd = ldd;
+    if (rows > 0 && cols > 0 &&
+        cudaMemcpy2DAsync(pe.dev, ldd * es, a, (size_t)d.ld * es, rows * es, cols, cudaMemcpyHostToDevice,
+                          pe.stream) != cudaSuccess)
+      die("host to device copy failed", -1);
+    if ((e = dlafb_cholesky_plan_run(pe.plan, pe.dev, ldd, pe.stream)) != 0)
+      die("factorization failed to launch", e);
+    if (rows > 0 && cols > 0 &&
+        cudaMemcpy2DAsync(a, (size_t)d.ld * es, pe.dev, ldd * es, rows * es, cols, cudaMemcpyDeviceToHost,
+                          pe.stream) != cudaSuccess)
+      die("device to host copy failed", -1);
+  }
+  if ((e = dlafb_cholesky_plan_info(pe.plan, &info)) != 0)
+    die("factorization failed", e);
+  if (cudaStreamSynchronize(pe.stream) != cudaSuccess)
+    die("stream synchronisation failed", -1);
+  return info;
+}
+
+void pxpotrf(char type, char uplo, int n, void* a, int ia, int ja, const int desca[9], int* info) {
+  if (desca[0] != 1)
+    die("only dense ScaLAPACK descriptors (desca[0] == 1) are supported", desca[0]);
+  if (ia != 1 || ja != 1)
+    die("ia and ja must be 1", ia);
+  const DLAF_descriptor d = make_dlaf_descriptor(n, n, ia - 1, ja - 1, desca);
+  const int r = cholesky(desca[1], type, uplo, a, d);
+  if (info)
+    *info = r;
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---- MPI shim ----
+MPI_Comm dlafb_mpi_comm_world(void) { return g_world; }
+
+int dlafb_mpi_init(int rank, int size, const void* id128) {
+  if (g_world)
+    return 0;
+  dlafb_mpi_comm* w = new dlafb_mpi_comm();
+  w->rank = rank;
+  w->size = size;
+  if (size > 1) {
+    if (!id128)
+      return -1;
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof(id));
+    const ncclResult_t r = ncclCommInitRank(&w->world, size, id, rank);
+    if (r != ncclSuccess) {
+      delete w;
+      return 1000 + (int)r;
+    }
+  }
+  g_world = w;
+  return 0;
+}
+
+int dlafb_mpi_finalize(void) {
+  if (g_world) {
+    if (g_world->world)
+      ncclCommDestroy(g_world->world);
+    delete g_world;
+    g_world = nullptr;
+  }
+  return 0;
+}
+
+int MPI_Comm_rank(MPI_Comm comm, int* rank) {
+  *rank = comm ? comm->rank : 0;
+  return MPI_SUCCESS;
+}
+int MPI_Comm_size(MPI_Comm comm, int* size) {
+  *size = comm ? comm->size : 1;
+  return MPI_SUCCESS;
+}
+
+// ---- init ----
+void dlaf_initialize(int, const char**, int argc_dlaf, const char** argv_dlaf) noexcept {
+  if (g_initialized)
+    return;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    die("no CUDA device: this library has no CPU fallback", -1);
+  for (int i = 0; i < argc_dlaf; ++i)
+    if (argv_dlaf && argv_dlaf[i] && std::strcmp(argv_dlaf[i], "--dlaf:print-config") == 0) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceProp p;
+      cudaGetDeviceProperties(&p, dev);
+      std::printf("DLA-Future (B200 build) configuration: device %d %s, %d SMs; look-ahead 1; panel workspaces 2\n",
+                  dev, p.name, p.multiProcessorCount);
+    }
+  g_initialized = true;
+}
+
+void dlaf_finalize(void) noexcept {
+  drop_plans_of(INT_MIN);
+  for (auto& kv : g_grids)
+    dlafb_grid_destroy(kv.second);
+  g_grids.clear();
+  g_initialized = false;
+}
+
+// ---- grids ----
+static dlafb_grid_t make_grid(MPI_Comm comm, int nprow, int npcol, char order) {
+  dlafb_grid_t g = nullptr;
+  int e;
+  const int size = comm ? comm->size : 1;
+  if (size != nprow * npcol)
+    die("grid size does not match the communicator size", size);
+  if (size == 1)
+    e = dlafb_grid_create_local(&g);
+  else
+    e = dlafb_grid_create_from_nccl(&g, comm->world, 0, comm->rank, size, nprow, npcol, order);
+  if (e != 0)
+    die("grid creation failed", e);
+  return g;
+}
+
+int dlaf_create_grid(MPI_Comm comm, int nprow, int npcol, char order) noexcept {
+  // contexts count down from INT_MAX so that they never collide with BLACS contexts (src/c_api/grid.cpp:28-40)
+  int ctx = INT_MAX - (int)g_grids.size();
+  while (g_grids.count(ctx))
+    --ctx;
+  g_grids[ctx] = make_grid(comm, nprow, npcol, order);
+  return ctx;
+}
+
+void dlaf_create_grid_from_blacs_info(int blacs_ctxt, MPI_Comm comm, int nprow, int npcol, char order) noexcept {
+  if (g_grids.count(blacs_ctxt)) {
+    drop_plans_of(blacs_ctxt);
+    dlafb_grid_destroy(g_grids[blacs_ctxt]);
+  }
+  g_grids[blacs_ctxt] = make_grid(comm, nprow, npcol, order);
+}
+
+void dlaf_free_grid(int context) noexcept {
+  auto it = g_grids.find(context);
+  if (it == g_grids.end())
+    return;
+  drop_plans_of(context);
+  dlafb_grid_destroy(it->second);
+  g_grids.erase(it);
+}
+
+char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow, int mypcol) noexcept {
+  // src/c_api/grid.cpp:45-70 decides by all-reducing two booleans; with the rank -> coordinate maps being
+  // deterministic the local test is enough when the grid is consistent.
+  const int rank = comm ? comm->rank : 0;
+  const bool row_major = (rank == myprow * npcol + mypcol);
+  const bool col_major = (rank == mypcol * nprow + myprow);
+  if (!row_major && !col_major)
+    die("grid_ordering: coordinates match neither row- nor column-major order", rank);
+  return col_major && !row_major ? 'C' : 'R';
+}
+
+struct DLAF_descriptor make_dlaf_descriptor(const int m, const int n, const int i, const int j,
+                                            const int desc[9]) noexcept {
+  if (i != 0 || j != 0)
+    die("make_dlaf_descriptor: sub-matrix offsets must be 0", i);
+  struct DLAF_descriptor d = {m, n, desc[4], desc[5], desc[6], desc[7], i, j, desc[8]};
+  return d;
+}
+
+// ---- factorization ----
+int dlaf_cholesky_factorization_s(const int ctx, const char uplo, float* a, const struct DLAF_descriptor d) noexcept {
+  return cholesky(ctx, 's', uplo, a, d);
+}
+int dlaf_cholesky_factorization_d(const int ctx, const char uplo, double* a, const struct DLAF_descriptor d) noexcept {
+  return cholesky(ctx, 'd', uplo, a, d);
+}
+int dlaf_cholesky_factorization_c(const int ctx, const char uplo, dlaf_complex_c* a,
+                                  const struct DLAF_descriptor d) noexcept {
+  return cholesky(ctx, 'c', uplo, a, d);
+}
+int dlaf_cholesky_factorization_z(const int ctx, const char uplo, dlaf_complex_z* a,
+                                  const struct DLAF_descriptor d) noexcept {
+  return cholesky(ctx, 'z', uplo, a, d);
+}
+void dlaf_pspotrf(const char uplo, const int n, float* a, const int ia, const int ja, const int desca[9],
+                  int* info) noexcept {
+  pxpotrf('s', uplo, n, a, ia, ja, desca, info);
+}
+void dlaf_pdpotrf(const char uplo, const int n, double* a, const int ia, const int ja, const int desca[9],
+                  int* info) noexcept {
+  pxpotrf('d', uplo, n, a, ia, ja, desca, info);
+}
+void dlaf_pcpotrf(const char uplo, const int n, dlaf_complex_c* a, const int ia, const int ja, const int desca[9],
+                  int* info) noexcept {
+  pxpotrf('c', uplo, n, a, ia, ja, desca, info);
+}
+void dlaf_pzpotrf(const char uplo, const int n, dlaf_complex_z* a, const int ia, const int ja, const int desca[9],
+                  int* info) noexcept {
+  pxpotrf('z', uplo, n, a, ia, ja, desca, info);
+}
+
+}  // extern "C"

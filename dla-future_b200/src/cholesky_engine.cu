@@ -1,0 +1,519 @@
+// Look-ahead scheduler of the distributed right-looking Cholesky over CUDA streams and NCCL.
+//
+// Role in the reference: Cholesky<Backend::GPU, Device::GPU, T>::call_L / call_U, local and distributed
+// (include/dlaf/factorization/cholesky/impl.h:150-452), together with the machinery it leans on there: pika
+// senders + per-tile async_rw_mutex for ordering, a CUDA stream pool with two priorities, RoundRobin<Panel>
+// workspaces (impl.h:218-221) and per-tile MPI_Ibcast with host staging. Here instead, per step k:
+//
+//   hp stream (high priority): POTRF(k,k) -> [bcast diag tile + its inverted blocks down the grid column]
+//        -> panel solve of column k -> [pack into the row panel, bcast along the row, bcasts of the
+//        transposed panel down the column] -> trailing update of global column k+1 only (look-ahead)
+//   np stream: trailing update of everything right of column k+1, one launch
+//
+// so POTRF/solve/broadcast of step k+1 overlap the bulk update of step k. Two panel buffers alternate
+// (the reference's n_workspaces = 2). Events express the only cross-stream dependencies:
+//   np(k) waits for the panels of step k; the hp update of step k waits for np(k-1).
+// The Upper variant runs the Lower algorithm on the conjugate-transposed local block (rows <-> columns of the
+// process grid swapped), with one HBM-speed transpose before and after.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <type_traits>
+#include <vector>
+
+#include "../../include/dlafb_engine.h"
+#include "gemm_dmma.cuh"
+#include "gemm_simt.cuh"
+#include "grid.h"
+#include "schedule.h"
+#include "tile_ops.cuh"
+
+using namespace dlafb;
+
+struct dlafb_chol_plan {
+  virtual ~dlafb_chol_plan() {}
+  virtual int run(void* a, int64_t lda, cudaStream_t stream) = 0;
+  virtual int info(int* out) = 0;
+  virtual void local_size(int64_t* r, int64_t* c) = 0;
+  virtual int profile(double* ms, double* flops, int* launches) = 0;
+  bool profiling = false;
+};
+
+namespace {
+
+#define CU(x)                    \
+  do {                           \
+    cudaError_t e_ = (x);        \
+    if (e_ != cudaSuccess)       \
+      return (int)e_;            \
+  } while (0)
+#define NC(x)                    \
+  do {                           \
+    ncclResult_t r_ = (x);       \
+    if (r_ != ncclSuccess)       \
+      return 1000 + (int)r_;     \
+  } while (0)
+
+template <class T>
+struct NcclType;
+template <>
+struct NcclType<float> {
+  static constexpr ncclDataType_t t = ncclFloat;
+  static constexpr int mult = 1;
+};
+template <>
+struct NcclType<double> {
+  static constexpr ncclDataType_t t = ncclDouble;
+  static constexpr int mult = 1;
+};
+template <>
+struct NcclType<float2> {
+  static constexpr ncclDataType_t t = ncclFloat;
+  static constexpr int mult = 2;
+};
+template <>
+struct NcclType<double2> {
+  static constexpr ncclDataType_t t = ncclDouble;
+  static constexpr int mult = 2;
+};
+
+inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+template <class T>
+struct Plan final : dlafb_chol_plan {
+  using R = typename Tr<T>::Real;
+
+  // configuration (L orientation: for uplo = 'U' rows and columns of the grid are swapped)
+  bool upper = false;
+  int64_t n = 0, nb = 1;
+  int P = 1, Q = 1, pr = 0, pc = 0;
+  ncclComm_t rowc = nullptr, colc = nullptr;
+  Schedule sched;
+  int64_t nt = 0, mloc = 0, nloc = 0;  // local rows / cols (L orientation)
+  bool dist = false;                   // more than one rank
+  bool fast = false;                   // TMA + DMMA path (double, nb % 128 == 0)
+  int ib = 64, nblk = 1;
+
+  cudaStream_t hp = nullptr, np = nullptr;
+  cudaEvent_t ev_in = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_np[2] = {nullptr, nullptr}, ev_hp_end = nullptr,
+              ev_np_end = nullptr;
+  T* D = nullptr;  // [inverted diagonal blocks (nblk*ib*ib) | diagonal tile (nb*nb, ld = nb)]
+  size_t d_elems = 0;
+  T* Pr[2] = {nullptr, nullptr};  // row panel: one nb x nb slot per local row tile
+  T* Pc[2] = {nullptr, nullptr};  // transposed panel: one slot per local column tile
+  CUtensorMap map_pr[2], map_pc[2];
+  int2* lists = nullptr;
+  std::vector<size_t> hp_off, np_off;
+  int* info_dev = nullptr;
+  T* tbuf = nullptr;  // transposed local block (Upper) or aligned mirror
+  int64_t ldt = 0;
+  // profiling of the bulk (np stream) update launches: one timed event pair per step
+  std::vector<cudaEvent_t> pev;
+  std::vector<double> np_flops;
+  std::vector<char> np_timed;
+
+  ~Plan() override {
+    cudaDeviceSynchronize();
+    if (hp) cudaStreamDestroy(hp);
+    if (np) cudaStreamDestroy(np);
+    for (cudaEvent_t e : {ev_in, ev_panel[0], ev_panel[1], ev_np[0], ev_np[1], ev_hp_end, ev_np_end})
+      if (e) cudaEventDestroy(e);
+    cudaFree(D);
+    for (int b = 0; b < 2; ++b) {
+      cudaFree(Pr[b]);
+      cudaFree(Pc[b]);
+    }
+    cudaFree(lists);
+    cudaFree(info_dev);
+    cudaFree(tbuf);
+    for (cudaEvent_t e : pev)
+      cudaEventDestroy(e);
+  }
+
+  // algorithmic flops of one update tile (real flops; complex multiply-add = 8)
+  double tile_flops(const UpdateTile& t) const {
+    const double r = (double)std::min<int64_t>(nb, mloc - t.row), c = (double)std::min<int64_t>(nb, nloc - t.col);
+    const double cm = Tr<T>::is_complex ? 4.0 : 1.0;
+    return cm * (t.diag ? r * (r + 1) * (double)nb : 2.0 * r * c * (double)nb);
+  }
+
+  int profile(double* ms, double* flops, int* launches) override {
+    CU(cudaStreamSynchronize(hp));
+    CU(cudaStreamSynchronize(np));
+    double t = 0, f = 0;
+    int l = 0;
+    for (int64_t k = 0; k < nt && 2 * k + 1 < (int64_t)pev.size(); ++k)
+      if (np_timed[k]) {
+        float x = 0;
+        CU(cudaEventElapsedTime(&x, pev[2 * k], pev[2 * k + 1]));
+        t += x;
+        f += np_flops[k];
+        ++l;
+      }
+    *ms = t;
+    *flops = f;
+    *launches = l;
+    return 0;
+  }
+
+  void local_size(int64_t* r, int64_t* c) override {
+    *r = upper ? nloc : mloc;
+    *c = upper ? mloc : nloc;
+  }
+
+  int init(dlafb_grid* g, char uplo, int64_t n_, int64_t nb_, int sr, int sc) {
+    upper = (uplo == 'U' || uplo == 'u');
+    n = n_;
+    nb = nb_;
+    if (!upper) {
+      P = g->P, Q = g->Q, pr = g->pr, pc = g->pc, rowc = g->row, colc = g->col;
+    }
+    else {
+      P = g->Q, Q = g->P, pr = g->pc, pc = g->pr, rowc = g->col, colc = g->row;
+      const int t = sr;
+      sr = sc;
+      sc = t;
+    }
+    dist = P * Q > 1;
+    sched = make_schedule(n, nb, P, Q, pr, pc, sr, sc);
+    nt = sched.rows.nt();
+    mloc = sched.rows.local_size();
+    nloc = sched.cols.local_size();
+    fast = std::is_same<T, double>::value && (nb % 128 == 0);
+    ib = fast ? 128 : 64;
+    nblk = (int)((nb + ib - 1) / ib);
+
+    int lo, hi;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi));
+    CU(cudaStreamCreateWithPriority(&np, cudaStreamNonBlocking, lo));
+    for (cudaEvent_t* e : {&ev_in, &ev_panel[0], &ev_panel[1], &ev_np[0], &ev_np[1], &ev_hp_end, &ev_np_end})
+      CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    CU(cudaMalloc(&info_dev, sizeof(int)));
+    CU(cudaMemset(info_dev, 0, sizeof(int)));
+    d_elems = (size_t)nblk * ib * ib + (size_t)nb * nb;
+    CU(cudaMalloc(&D, d_elems * sizeof(T)));
+    CU(cudaMemset(D, 0, d_elems * sizeof(T)));
+    if (dist) {
+      const size_t rt = (size_t)sched.rows.nloc_tiles(), ct = (size_t)sched.cols.nloc_tiles();
+      for (int b = 0; b < 2; ++b) {
+        CU(cudaMalloc(&Pr[b], (rt + 1) * nb * nb * sizeof(T)));
+        CU(cudaMalloc(&Pc[b], (ct + 1) * nb * nb * sizeof(T)));
+        CU(cudaMemset(Pr[b], 0, (rt + 1) * nb * nb * sizeof(T)));
+        CU(cudaMemset(Pc[b], 0, (ct + 1) * nb * nb * sizeof(T)));
+        if (fast) {
+          if (rt && make_operand_map(&map_pr[b], (const double*)Pr[b], (long long)rt * nb, nb, nb, 4) != 0)
+            return -2;
+          if (ct && make_operand_map(&map_pc[b], (const double*)Pc[b], (long long)ct * nb, nb, nb, 4) != 0)
+            return -2;
+        }
+      }
+    }
+    // update lists of all steps, uploaded once
+    std::vector<int2> all;
+    hp_off.assign(nt + 1, 0);
+    np_off.assign(nt + 1, 0);
+    for (int64_t k = 0; k < nt; ++k) {
+      const Step& st = sched.steps[k];
+      hp_off[k] = all.size();
+      for (const UpdateTile& t : st.hp)
+        all.push_back(make_int2(t.row, t.col | (t.diag ? (int)0x80000000 : 0)));
+      np_off[k] = all.size();
+      for (const UpdateTile& t : st.np)
+        all.push_back(make_int2(t.row, t.col | (t.diag ? (int)0x80000000 : 0)));
+    }
+    if (!all.empty()) {
+      CU(cudaMalloc(&lists, all.size() * sizeof(int2)));
+      CU(cudaMemcpy(lists, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    }
+    np_flops.assign(nt + 1, 0.0);
+    for (int64_t k = 0; k < nt; ++k)
+      for (const UpdateTile& t : sched.steps[k].np)
+        np_flops[k] += tile_flops(t);
+    if (upper) {
+      ldt = round_up(mloc > 0 ? mloc : 1, 64);
+      CU(cudaMalloc(&tbuf, ((size_t)ldt * (nloc > 0 ? nloc : 1) + 64) * sizeof(T)));
+    }
+    return 0;
+  }
+
+  // trailing update of the listed tiles: C(tile) -= rowpanel * colpanel^H
+  int update(cudaStream_t s, T* A, int64_t ld, const CUtensorMap* map_a_local, int nbox_local, int64_t k, int buf,
+             size_t off, size_t count) {
+    if (count == 0)
+      return 0;
+    if (fast) {
+      GemmParams p{};
+      p.C = reinterpret_cast<double*>(A);
+      p.ldc = ld;
+      p.m_total = (int)mloc;
+      p.n_total = (int)nloc;
+      p.K = (int)nb;
+      p.alpha = -1.0;
+      p.beta = 1.0;
+      p.list = lists + off;
+      p.sub = (int)(nb / kBM);
+      p.tile = (int)nb;
+      if (dist) {
+        p.nbox_a = p.nbox_b = 4;
+        return (int)launch_gemm_nt_dmma(s, map_pr[buf], map_pc[buf], p, (unsigned)(count * p.sub * p.sub), 1);
+      }
+      p.a_col0 = p.b_col0 = (int)(k * nb);
+      p.nbox_a = p.nbox_b = nbox_local;
+      return (int)launch_gemm_nt_dmma(s, *map_a_local, *map_a_local, p, (unsigned)(count * p.sub * p.sub), 1);
+    }
+    SimtParams<T> p{};
+    p.C = A;
+    p.ldc = ld;
+    p.m_total = (int)mloc;
+    p.n_total = (int)nloc;
+    p.K = (int)nb;
+    p.alpha = R(-1);
+    p.beta = R(1);
+    p.list = lists + off;
+    p.sub = (int)((nb + kSimtTile - 1) / kSimtTile);
+    p.tile = (int)nb;
+    if (dist) {
+      p.A = Pr[buf];
+      p.B = Pc[buf];
+      p.lda = p.ldb = nb;
+      p.a_tiled = p.b_tiled = 1;
+    }
+    else {
+      p.A = A + (size_t)k * nb * ld;
+      p.B = p.A;
+      p.lda = p.ldb = ld;
+    }
+    return (int)launch_gemm_simt<T>(s, p, (unsigned)(count * p.sub * p.sub), 1);
+  }
+
+  int factor_lower(T* A, int64_t ld) {
+    CUtensorMap map_local;
+    int nbox_local = 1;
+    if (fast && !dist && n > 0) {
+      // rank-3 view reads whole 16-row groups: fine when the rows are a multiple of 16 or the columns are padded
+      const int kind = (mloc % 16 == 0 || ld >= round_up(mloc, 16)) ? 3 : 2;
+      int r = make_operand_map(&map_local, (const double*)A, mloc, nloc, ld, kind);
+      nbox_local = kind == 3 ? 1 : 8;
+      if (r != 0 && kind == 3) {
+        r = make_operand_map(&map_local, (const double*)A, mloc, nloc, ld, 2);
+        nbox_local = 8;
+      }
+      if (r != 0)
+        return -2;
+    }
+    T* DW = D;
+    T* DL = D + (size_t)nblk * ib * ib;
+    const ncclDataType_t nt_ = NcclType<T>::t;
+    const size_t mult = NcclType<T>::mult;
+    const size_t slot = (size_t)nb * nb;
+
+    for (int64_t k = 0; k < nt; ++k) {
+      const Step& st = sched.steps[k];
+      const int buf = (int)(k & 1);
+      const int nk = (int)sched.rows.tile_size(k);
+      const bool last = (k == nt - 1);
+      T* Akk = nullptr;
+      if (st.own_diag) {
+        Akk = A + (size_t)st.lk_row * nb + (size_t)st.lk_col * nb * ld;
+        CU(potrf_tile<T>(hp, 'L', nk, Akk, ld, DW, ib, info_dev, (int)(k * nb)));
+      }
+      if (!last) {
+        if (!dist) {
+          const int m_below = (int)(n - (k + 1) * nb);
+          CU(trsm_panel<T>(hp, (int)nb, Akk, ld, DW, ib, A + (size_t)(k + 1) * nb + (size_t)k * nb * ld, ld, m_below));
+        }
+        else {
+          if (st.in_col) {
+            if (P > 1) {
+              if (st.own_diag)
+                CU(lacpy<T>(hp, 'L', (int)nb, (int)nb, Akk, ld, DL, nb));
+              NC(ncclBroadcast(D, D, d_elems * mult, nt_, st.diag_root, colc, hp));
+            }
+            const T* Lkk = (P > 1) ? DL : Akk;
+            const int64_t ldl = (P > 1) ? nb : ld;
+            const int m_below = (int)(mloc - (int64_t)st.il0 * nb);
+            if (m_below > 0) {
+              T* B = A + (size_t)st.il0 * nb + (size_t)st.lk_col * nb * ld;
+              CU(trsm_panel<T>(hp, (int)nb, Lkk, ldl, DW, ib, B, ld, m_below));
+              CU(pack_tiles<T>(hp, m_below, (int)nb, B, ld, Pr[buf] + (size_t)st.il0 * slot, (int)nb));
+            }
+          }
+          const size_t row_cnt = (size_t)(st.il_end - st.il0) * slot;
+          if (Q > 1 && row_cnt > 0) {
+            T* p = Pr[buf] + (size_t)st.il0 * slot;
+            NC(ncclBroadcast(p, p, row_cnt * mult, nt_, st.row_root, rowc, hp));
+          }
+          if (!st.colb.empty()) {
+            if (P > 1) {
+              NC(ncclGroupStart());
+              for (const ColBcast& cb : st.colb) {
+                T* recv = Pc[buf] + (size_t)cb.jl * slot;
+                const T* send = (cb.root == pr) ? Pr[buf] + (size_t)cb.src_il * slot : recv;
+                NC(ncclBroadcast(send, recv, slot * mult, nt_, cb.root, colc, hp));
+              }
+              NC(ncclGroupEnd());
+            }
+            else {
+              for (const ColBcast& cb : st.colb)
+                CU(cudaMemcpyAsync(Pc[buf] + (size_t)cb.jl * slot, Pr[buf] + (size_t)cb.src_il * slot,
+                                   slot * sizeof(T), cudaMemcpyDeviceToDevice, hp));
+            }
+          }
+        }
+        CU(cudaEventRecord(ev_panel[buf], hp));
+        // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
+        if (k >= 1)
+          CU(cudaStreamWaitEvent(hp, ev_np[(k - 1) & 1], 0));
+        int r = update(hp, A, ld, &map_local, nbox_local, k, buf, hp_off[k], np_off[k] - hp_off[k]);
+        if (r != 0)
+          return r;
+        CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
+        const size_t np_cnt = (k + 1 < nt ? hp_off[k + 1] : np_off[k]) - np_off[k];
+        const bool timed = profiling && np_cnt > 0;
+        if (timed)
+          CU(cudaEventRecord(pev[2 * k], np));
+        r = update(np, A, ld, &map_local, nbox_local, k, buf, np_off[k], np_cnt);
+        if (r != 0)
+          return r;
+        if (timed)
+          CU(cudaEventRecord(pev[2 * k + 1], np));
+        np_timed[k] = timed;
+        CU(cudaEventRecord(ev_np[buf], np));
+      }
+    }
+    return 0;
+  }
+
+  int run(void* a_, int64_t lda, cudaStream_t user) override {
+    T* a = static_cast<T*>(a_);
+    if (profiling && pev.empty()) {
+      pev.resize(2 * nt);
+      for (cudaEvent_t& e : pev)
+        CU(cudaEventCreate(&e));
+    }
+    np_timed.assign(nt + 1, 0);
+    CU(cudaEventRecord(ev_in, user));
+    CU(cudaStreamWaitEvent(hp, ev_in, 0));
+    CU(cudaStreamWaitEvent(np, ev_in, 0));
+    CU(cudaMemsetAsync(info_dev, 0, sizeof(int), hp));
+    int r = 0;
+    if (n > 0) {
+      if (!upper) {
+        const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(a) & 15) || (lda & 1));
+        if (misaligned) {
+          if (!tbuf) {
+            ldt = round_up(mloc > 0 ? mloc : 1, 64);
+            CU(cudaMalloc(&tbuf, ((size_t)ldt * (nloc > 0 ? nloc : 1) + 64) * sizeof(T)));
+          }
+          CU(lacpy<T>(hp, 'G', (int)mloc, (int)nloc, a, lda, tbuf, ldt));
+          r = factor_lower(tbuf, ldt);
+          if (r == 0) {
+            CU(cudaStreamWaitEvent(hp, ev_np[0], 0));
+            CU(cudaStreamWaitEvent(hp, ev_np[1], 0));
+            CU(lacpy<T>(hp, 'G', (int)mloc, (int)nloc, tbuf, ldt, a, lda));
+          }
+        }
+        else {
+          r = factor_lower(a, lda);
+        }
+      }
+      else {
+        // local block of A is nloc x mloc in the caller's orientation; its conjugate transpose is mloc x nloc
+        CU(transpose<T>(hp, (int)nloc, (int)mloc, a, lda, tbuf, ldt, 1, 'G'));
+        r = factor_lower(tbuf, ldt);
+        if (r == 0) {
+          CU(cudaStreamWaitEvent(hp, ev_np[0], 0));
+          CU(cudaStreamWaitEvent(hp, ev_np[1], 0));
+          CU(transpose<T>(hp, (int)mloc, (int)nloc, tbuf, ldt, a, lda, 1, 'G'));
+        }
+      }
+    }
+    CU(cudaEventRecord(ev_hp_end, hp));
+    CU(cudaEventRecord(ev_np_end, np));
+    CU(cudaStreamWaitEvent(user, ev_hp_end, 0));
+    CU(cudaStreamWaitEvent(user, ev_np_end, 0));
+    return r;
+  }
+
+  int info(int* out) override {
+    CU(cudaStreamSynchronize(hp));
+    CU(cudaStreamSynchronize(np));
+    int v = 0;
+    CU(cudaMemcpy(&v, info_dev, sizeof(int), cudaMemcpyDeviceToHost));
+    *out = v;
+    return 0;
+  }
+};
+
+template <class T>
+int create(dlafb_chol_plan_t* out, dlafb_grid* g, char uplo, int64_t n, int64_t nb, int sr, int sc) {
+  Plan<T>* p = new Plan<T>();
+  const int r = p->init(g, uplo, n, nb, sr, sc);
+  if (r != 0) {
+    delete p;
+    return r;
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dlafb_cholesky_plan_create(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char type, char uplo, int64_t n,
+                               int64_t nb, int src_r, int src_c) {
+  if (!plan || !grid || n < 0 || nb < 1 || n > 0x7fffff00ll)
+    return -1;
+  if (src_r < 0 || src_r >= grid->P || src_c < 0 || src_c >= grid->Q)
+    return -1;
+  switch (type) {
+    case 's': return create<float>(plan, grid, uplo, n, nb, src_r, src_c);
+    case 'd': return create<double>(plan, grid, uplo, n, nb, src_r, src_c);
+    case 'c': return create<float2>(plan, grid, uplo, n, nb, src_r, src_c);
+    case 'z': return create<double2>(plan, grid, uplo, n, nb, src_r, src_c);
+  }
+  return -1;
+}
+
+int dlafb_cholesky_plan_run(dlafb_chol_plan_t plan, void* a, int64_t lda, void* stream) {
+  if (!plan)
+    return -1;
+  return plan->run(a, lda, static_cast<cudaStream_t>(stream));
+}
+
+int dlafb_cholesky_plan_info(dlafb_chol_plan_t plan, int* info) {
+  if (!plan || !info)
+    return -1;
+  return plan->info(info);
+}
+
+int dlafb_cholesky_plan_set_profiling(dlafb_chol_plan_t plan, int on) {
+  if (!plan)
+    return -1;
+  plan->profiling = on != 0;
+  return 0;
+}
+
+int dlafb_cholesky_plan_profile(dlafb_chol_plan_t plan, double* update_ms, double* update_flops, int* launches) {
+  if (!plan || !update_ms || !update_flops || !launches)
+    return -1;
+  return plan->profile(update_ms, update_flops, launches);
+}
+
+int dlafb_cholesky_plan_destroy(dlafb_chol_plan_t plan) {
+  delete plan;
+  return 0;
+}
+
+int dlafb_cholesky_plan_local_size(dlafb_chol_plan_t plan, int64_t* rows, int64_t* cols) {
+  if (!plan || !rows || !cols)
+    return -1;
+  plan->local_size(rows, cols);
+  return 0;
+}
+
+}  // extern "C"

@@ -92,7 +92,12 @@ def cholesky_setters(n, uplo, dtype, rows=None, cols=None):
     cols = np.arange(n) if cols is None else np.asarray(cols)
     i = rows[:, None].astype(np.float64)
     j = cols[None, :].astype(np.float64)
-    mag_a = np.exp2(-(i + j)) / 3 * (np.exp2(2 * (np.minimum(i, j) + 1)) - 1)
+    mn = np.minimum(i, j)
+    with np.errstate(over="ignore", invalid="ignore"):
+        mag_a = np.exp2(-(i + j)) / 3 * (np.exp2(2 * (mn + 1)) - 1)
+    # The reference expression overflows double for min(i,j) >= 511 (its own tests stop at n = 128); beyond that
+    # the same value is formed as (2^(2min+2-i-j) - 2^-(i+j)) / 3, which has no large intermediate.
+    mag_a = np.where(2 * (mn + 1) < 1000, mag_a, (np.exp2(2 * mn + 2 - i - j) - np.exp2(-(i + j))) / 3)
     mag_t = np.exp2(-np.abs(i - j))
     if dtype.kind == "c":
         ph = np.exp(1j * (j - i))
