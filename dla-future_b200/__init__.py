@@ -48,11 +48,26 @@ def declared_symbols():
             _c_api.symbols())
 
 
+def _preload_nccl():
+    """libdlaf_b200.so needs libnccl.so.2. When torch is installed its bundled NCCL must be the one in the process
+    (libtorch_cuda.so needs symbols newer than the system copy has), so load that one first."""
+    import glob
+    import sys
+    for base in sys.path:
+        for cand in glob.glob(os.path.join(base, "nvidia", "nccl", "lib", "libnccl.so.2")):
+            try:
+                ctypes.CDLL(cand, mode=ctypes.RTLD_GLOBAL)
+                return
+            except OSError:
+                pass
+
+
 def lib():
     global _LIB
     if _LIB is None:
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(f"{LIB_PATH} not built: run `make` (or __graft_entry__.build()); no CPU fallback")
+        _preload_nccl()
         L = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
         for k, (res, args) in TILE_API.items():
             for x in TYPES:

@@ -113,44 +113,55 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 
   const int nk = p.K / kBK;
 
-  if (warp == 8) {
-    // ---- TMA producer: one lane feeds the ring of stages ----
-    if (lane == 0) {
-      const int a_row = row0 + p.a_row_off;
-      const int b_row = b_from_a ? b_row_a : col0 + p.b_row_off;
-      const CUtensorMap* mb = b_from_a ? &map_a : &map_b;
-      const int nbox_b = b_from_a ? p.nbox_a : p.nbox_b;
-      const int b_col0 = b_from_a ? p.a_col0 : p.b_col0;
-      for (int kt = 0; kt < nk; ++kt) {
-        const int s = kt % kStages;
-        const uint32_t ph = (kt / kStages) & 1;
-        mbar_wait(bar_empty + 8 * s, ph ^ 1);
-        const uint32_t full = bar_full + 8 * s;
-        mbar_expect_tx(full, kStageBytes);
-        const uint32_t sa = base + s * kStageBytes;
-        const uint32_t sb = sa + kOperandStageBytes;
-        const int ka = p.a_col0 + kt * kBK;
-        const int kb = b_col0 + kt * kBK;
-        if (p.nbox_a == 1)
-          tma_load_3d(sa, &map_a, 0, ka, a_row >> 4, full);
-        else if (p.nbox_a == 4)
-          tma_load_4d(sa, &map_a, 0, ka, (a_row % p.tile) >> 4, a_row / p.tile, full);
-        else
-          for (int g = 0; g < 8; ++g)
-            tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
-        if (nbox_b == 1)
-          tma_load_3d(sb, mb, 0, kb, b_row >> 4, full);
-        else if (nbox_b == 4)
-          tma_load_4d(sb, mb, 0, kb, (b_row % p.tile) >> 4, b_row / p.tile, full);
-        else
-          for (int g = 0; g < 8; ++g)
-            tma_load_2d(sb + g * kGroupBytes, mb, b_row + 16 * g, kb, full);
-      }
+  // ---- pull this block of C into L2 while the contraction runs (the epilogue reads it) ----
+  if (p.beta != 0.0) {
+    const int rows = min(kBM, m_lim - row0);
+    const int cols = min(kBN, n_lim - col0);
+    const int segs = (rows + 15) >> 4;  // 128-byte lines per column
+    for (int i = threadIdx.x; i < cols * segs; i += kGemmThreads) {
+      const int c = i / segs, sgm = i - c * segs;
+      const double* ptr = p.C + (long long)(col0 + c) * p.ldc + row0 + sgm * 16;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
     }
-    return;
   }
 
-  // ---- DMMA consumers: 8 warps as 2 (rows) x 4 (cols); each owns a 64 x 32 block of C ----
+  // ---- TMA producer role: lane 0 of warp 0 feeds the ring of stages, kPrefetch slices ahead of the math ----
+  const bool producer = (threadIdx.x == 0);
+  const int a_row = row0 + p.a_row_off;
+  const int b_row = b_from_a ? b_row_a : col0 + p.b_row_off;
+  const CUtensorMap* mb = b_from_a ? &map_a : &map_b;
+  const int nbox_b = b_from_a ? p.nbox_a : p.nbox_b;
+  const int b_col0 = b_from_a ? p.a_col0 : p.b_col0;
+  auto issue = [&](int kt) {
+    const int s = kt % kStages;
+    const uint32_t ph = (kt / kStages) & 1;
+    mbar_wait(bar_empty + 8 * s, ph ^ 1);
+    const uint32_t full = bar_full + 8 * s;
+    mbar_expect_tx(full, kStageBytes);
+    const uint32_t sa = base + s * kStageBytes;
+    const uint32_t sb = sa + kOperandStageBytes;
+    const int ka = p.a_col0 + kt * kBK;
+    const int kb = b_col0 + kt * kBK;
+    if (p.nbox_a == 1)
+      tma_load_3d(sa, &map_a, 0, ka, a_row >> 4, full);
+    else if (p.nbox_a == 4)
+      tma_load_4d(sa, &map_a, 0, ka, (a_row % p.tile) >> 4, a_row / p.tile, full);
+    else
+      for (int g = 0; g < 8; ++g)
+        tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
+    if (nbox_b == 1)
+      tma_load_3d(sb, mb, 0, kb, b_row >> 4, full);
+    else if (nbox_b == 4)
+      tma_load_4d(sb, mb, 0, kb, (b_row % p.tile) >> 4, b_row / p.tile, full);
+    else
+      for (int g = 0; g < 8; ++g)
+        tma_load_2d(sb + g * kGroupBytes, mb, b_row + 16 * g, kb, full);
+  };
+  if (producer)
+    for (int kt = 0; kt < kPrefetch && kt < nk; ++kt)
+      issue(kt);
+
+  // ---- DMMA: 8 warps as 2 (rows) x 4 (cols); each owns a 64 x 32 block of C ----
   const int wm = warp & 1;
   const int wn = warp >> 1;
   const int r = lane >> 2;   // fragment row (A) / column (B)
@@ -175,6 +186,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   const uint32_t b_thr = kOperandStageBytes + (wn * 2) * kGroupBytes + (2 * kk) * 128;
 
   for (int kt = 0; kt < nk; ++kt) {
+    // refill the stage freed two slices ago: its empty barrier is (almost always) already complete
+    if (producer && kt + kPrefetch < nk)
+      issue(kt + kPrefetch);
     const int s = kt % kStages;
     const uint32_t ph = (kt / kStages) & 1;
     mbar_wait(bar_full + 8 * s, ph);
@@ -203,6 +217,44 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   // ---- epilogue: C <- beta*C + alpha*acc, clipped and (optionally) restricted to the lower triangle ----
   const double alpha = p.alpha, beta = p.beta;
   const bool full_block = !lower || (trow >= tcol + kBN - 1);
+  if (full_block && row0 + kBM <= m_lim && col0 + kBN <= n_lim) {
+    // interior block: no predicates; the 16 loads of column group g+1 are in flight while group g is stored
+    double* cb = p.C + (long long)(col0 + wn * 32 + 2 * kk) * p.ldc + (row0 + wm * 64 + r);
+    const long long ldc = p.ldc;
+    if (beta != 0.0) {
+      double cv[2][2][8];
+#pragma unroll
+      for (int e = 0; e < 2; ++e)
+#pragma unroll
+        for (int f = 0; f < 8; ++f)
+          cv[0][e][f] = __ldcg(cb + e * ldc + f * 8);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        if (g + 1 < 4) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int f = 0; f < 8; ++f)
+              cv[(g + 1) & 1][e][f] = __ldcg(cb + ((g + 1) * 8 + e) * ldc + f * 8);
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int f = 0; f < 8; ++f)
+            __stcg(cb + (g * 8 + e) * ldc + f * 8, fma(beta, cv[g & 1][e][f], alpha * acc[f][g][e]));
+      }
+    }
+    else {
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int f = 0; f < 8; ++f)
+            __stcg(cb + (g * 8 + e) * ldc + f * 8, alpha * acc[f][g][e]);
+    }
+    return;
+  }
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
 #pragma unroll

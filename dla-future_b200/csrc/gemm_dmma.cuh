@@ -21,7 +21,8 @@ constexpr int kGroupBytes = kBK * 128;             // one 16-row group of one K-
 constexpr int kOperandStageBytes = kBM * kBK * 8;  // 16 KiB
 constexpr int kStageBytes = 2 * kOperandStageBytes;
 constexpr int kGemmSmemBytes = kStages * kStageBytes + 2 * kStages * 8 + 1024;  // + barriers + align slack
-constexpr int kGemmThreads = 288;  // 8 DMMA warps + 1 TMA warp
+constexpr int kGemmThreads = 256;  // 8 DMMA warps; lane 0 of warp 0 also issues the TMA loads
+constexpr int kPrefetch = kStages - 2;  // slices in flight ahead of the math (refills the stage freed two slices ago)
 
 struct GemmParams {
   double* C;

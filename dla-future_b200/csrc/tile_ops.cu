@@ -19,7 +19,7 @@ bool dmma_ok(int, int, const T*, long long, const T*, long long, int) {
 }
 template <>
 bool dmma_ok<double>(int M, int N, const double* A, long long lda, const double* B, long long ldb, int K) {
-  return M >= 16 && N >= 16 && K > 0 && (K % kBK) == 0 && aligned16(A) && aligned16(B) && (lda % 2) == 0 &&
+  return M >= 1 && N >= 1 && K > 0 && (K % kBK) == 0 && aligned16(A) && aligned16(B) && (lda % 2) == 0 &&
          (ldb % 2) == 0;
 }
 

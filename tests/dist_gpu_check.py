@@ -1,0 +1,134 @@
+"""Multi-GPU parity check of the distributed factorization, one process per GPU (run under torchrun; started by
+tests/test_cholesky_dist_gpu.py or by hand):
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+      tests/dist_gpu_check.py
+
+Cases follow test/unit/factorization/test_cholesky.cpp:54-139 (distributed part): the reference sizes with the
+analytical known answer and a non-zero source rank, on every P x Q factorisation of the world size, both uplo,
+four element types, through both the engine ABI (device pointers) and the C API (dlaf_p?potrf, host pointers);
+plus larger seeded random HPD matrices on the TMA + DMMA path checked against the oracle factor.
+Every rank builds the same global matrix on the host, factorizes its own block on its GPU and compares its block.
+"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+from conftest import load_package  # noqa: E402
+import dlaf_oracle as orc  # noqa: E402
+
+NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
+REF_SIZES = [(0, 2), (5, 8), (34, 34), (4, 3), (16, 10), (34, 13), (32, 5)]
+
+
+def new_uid(L, rank):
+    buf = ctypes.create_string_buffer(128)
+    if rank == 0:
+        assert L.dlafb_nccl_unique_id(buf) == 0
+    t = torch.tensor(list(buf.raw), dtype=torch.uint8, device="cuda")
+    dist.broadcast(t, 0)
+    return bytes(t.cpu().tolist())
+
+
+def local_index(L, n, nb, P, rank, src):
+    tiles = [L.dlafb_dist_global_tile_from_local(l, P, rank, src)
+             for l in range(L.dlafb_dist_local_nr_tiles(n, nb, P, rank, src))]
+    idx = [np.arange(g * nb, min(n, (g + 1) * nb)) for g in tiles] + [np.arange(0)]
+    return np.concatenate(idx).astype(int)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = load_package()
+    L = pkg.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    failures, ncases = [], 0
+    grids = [(p, world // p) for p in range(1, world + 1) if world % p == 0]
+    L.dlaf_initialize(0, None, 0, None)
+    assert L.dlafb_mpi_init(rank, world, ctypes.create_string_buffer(new_uid(L, rank), 128)) == 0
+
+    for gi, (P, Q) in enumerate(grids):
+        for order in ("R", "C"):
+            grid = pkg.Grid(L, P, Q, rank, world, new_uid(L, rank), order)
+            ctx = 100 + 2 * gi + (order == "C")
+            L.dlaf_create_grid_from_blacs_info(ctx, L.dlafb_mpi_comm_world(), P, Q, order.encode())
+            src = (max(0, P - 1), min(1, Q - 1))
+
+            def run_case(x, uplo, n, nb, a_glob, expect, tol, what, use_c_api):
+                rows = local_index(L, n, nb, P, grid.pr, src[0])
+                cols = local_index(L, n, nb, Q, grid.pc, src[1])
+                loc = np.asfortranarray(a_glob[np.ix_(rows, cols)])
+                ld = max(1, len(rows)) + 3
+                host = np.full((max(1, len(cols)), ld), -7.7, dtype=a_glob.dtype)
+                host[:len(cols), :len(rows)] = loc.T
+                if use_c_api:
+                    desca = pkg.DESC9(1, ctx, n, n, nb, nb, src[0], src[1], ld)
+                    info = ctypes.c_int(-1)
+                    getattr(L, f"dlaf_p{x}potrf")(uplo.encode(), n, host.ctypes.data, 1, 1, desca, ctypes.byref(info))
+                    out, inf = host, info.value
+                else:
+                    plan = pkg.CholeskyPlan(L, grid, x, uplo, n, nb, src)
+                    assert (plan.local_rows, plan.local_cols) == (len(rows), len(cols))
+                    dev = torch.from_numpy(host.reshape(-1).copy()).cuda()
+                    plan.run(dev.data_ptr(), ld, stream)
+                    inf = plan.info()
+                    torch.cuda.synchronize()
+                    out = dev.cpu().numpy().reshape(host.shape)
+                    plan.close()
+                got = np.ascontiguousarray(out[:len(cols), :len(rows)].T)
+                bad = orc.check_near(got, expect[np.ix_(rows, cols)], tol, tol) if got.size else 0
+                pad_ok = bool(np.all(out[:len(cols), len(rows):] == a_glob.dtype.type(-7.7)))
+                return (inf != 0) or bad > 0 or not pad_ok, f"{what} info={inf} bad={bad} pad_ok={pad_ok}"
+
+            for x in "sdcz":
+                for uplo in "LU":
+                    for (m, mb) in REF_SIZES:
+                        a, t = orc.cholesky_setters(m, uplo, NP[x])
+                        tol = 4 * (m + 1) * orc.type_error(NP[x])
+                        for capi in (False, True):
+                            if capi and (order == "C" and x in "sc"):
+                                continue
+                            fail, msg = run_case(x, uplo, m, mb, a, t, tol,
+                                                 f"analytic {x} {uplo} m={m} mb={mb} grid={P}x{Q}{order} capi={capi}", capi)
+                            ncases += 1
+                            if fail:
+                                failures.append(msg)
+            if order == "R":
+                for x, n, nb in [("d", 2048, 128), ("d", 1664, 256), ("d", 1100, 128), ("z", 640, 64), ("s", 768, 128)]:
+                    for uplo in "LU":
+                        a = orc.gen_hpd(n, nb, NP[x])
+                        ref = a.copy(order="F")
+                        assert orc.cholesky_local(uplo, ref, nb) == 0
+                        eps = np.finfo(NP[x]).eps
+                        tol = 50 * n * eps * np.sqrt(2.0)
+                        fail, msg = run_case(x, uplo, n, nb, a, ref, tol,
+                                             f"random {x} {uplo} n={n} nb={nb} grid={P}x{Q}", False)
+                        ncases += 1
+                        if fail:
+                            failures.append(msg)
+            L.dlaf_free_grid(ctx)
+            grid.close()
+
+    L.dlaf_finalize()
+    flag = torch.tensor([len(failures)], device="cuda")
+    dist.all_reduce(flag)
+    if failures:
+        print(f"[rank {rank}] {len(failures)} of {ncases} FAILED:\n  " + "\n  ".join(failures[:20]), flush=True)
+    if rank == 0:
+        print(f"dist_gpu_check world={world} grids={grids} cases={ncases} total_failures={int(flag.item())}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if int(flag.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()

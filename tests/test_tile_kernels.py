@@ -110,7 +110,7 @@ def test_potrf_tile_inverse_blocks(L, x, n):
 # -------------------------------------------------------------------------------------------- gemm
 GEMM_SIZES = [(0, 0, 0, 0), (7, 0, 2, 3), (0, 5, 2, 1), (1, 1, 0, 0), (3, 2, 7, 1), (12, 20, 11, 3), (8, 8, 11, 0),
               (128, 128, 128, 5),  # reference: up to 128^3 with padded ld
-              (256, 256, 128, 0), (384, 128, 128, 0), (200, 136, 64, 0), (130, 270, 48, 2), (512, 512, 512, 0)]
+              (8, 24, 16, 0), (10, 128, 128, 0), (256, 256, 128, 0), (384, 128, 128, 0), (200, 136, 64, 0), (130, 270, 48, 2), (512, 512, 512, 0)]
 
 
 @pytest.mark.parametrize("x", TYPES)
@@ -155,7 +155,7 @@ def test_herk_lower(L, x, n, k, extra):
 
 # -------------------------------------------------------------------------------------------- trsm
 @pytest.mark.parametrize("x", TYPES)
-@pytest.mark.parametrize("m,nk,extra", [(0, 1, 0), (1, 1, 0), (3, 7, 1), (13, 32, 2), (50, 64, 0), (64, 128, 0),
+@pytest.mark.parametrize("m,nk,extra", [(0, 1, 0), (1, 1, 0), (3, 7, 1), (10, 128, 0), (13, 32, 2), (50, 64, 0), (64, 128, 0),
                                         (300, 128, 0), (1000, 256, 0), (384, 512, 0), (100, 200, 3)])
 def test_trsm_panel(L, x, m, nk, extra):
     """B <- B L^-H (Right, Lower, ConjTrans, NonUnit, alpha 1; impl.h:55-67) after potrf of the diagonal tile."""
