@@ -26,6 +26,9 @@ import dlaf_oracle as orc  # noqa: E402
 
 NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
 REF_SIZES = [(0, 2), (5, 8), (34, 34), (4, 3), (16, 10), (34, 13), (32, 5)]
+QUICK = os.environ.get("DLAFB_DIST_QUICK") == "1"   # fewer types / sizes: for large world sizes
+TYPES = "dz" if QUICK else "sdcz"
+SIZES = [(0, 2), (34, 13), (32, 5)] if QUICK else REF_SIZES
 
 
 def new_uid(L, rank):
@@ -89,9 +92,9 @@ def main():
                 pad_ok = bool(np.all(out[:len(cols), len(rows):] == a_glob.dtype.type(-7.7)))
                 return (inf != 0) or bad > 0 or not pad_ok, f"{what} info={inf} bad={bad} pad_ok={pad_ok}"
 
-            for x in "sdcz":
+            for x in TYPES:
                 for uplo in "LU":
-                    for (m, mb) in REF_SIZES:
+                    for (m, mb) in SIZES:
                         a, t = orc.cholesky_setters(m, uplo, NP[x])
                         tol = 4 * (m + 1) * orc.type_error(NP[x])
                         for capi in (False, True):
@@ -103,7 +106,8 @@ def main():
                             if fail:
                                 failures.append(msg)
             if order == "R":
-                for x, n, nb in [("d", 2048, 128), ("d", 1664, 256), ("d", 1100, 128), ("z", 640, 64), ("s", 768, 128)]:
+                big = [("d", 4096, 128), ("d", 1100, 128)] if QUICK else [("d", 2048, 128), ("d", 1664, 256), ("d", 1100, 128), ("z", 640, 64), ("s", 768, 128)]
+                for x, n, nb in big:
                     for uplo in "LU":
                         a = orc.gen_hpd(n, nb, NP[x])
                         ref = a.copy(order="F")
