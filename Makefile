@@ -33,7 +33,7 @@ miniapp: $(BINDIR)/miniapp_cholesky
 
 $(BINDIR)/miniapp_cholesky: miniapp/miniapp_cholesky.cpp $(LIBDIR)/libdlaf_b200.so $(HDRS)
 	@mkdir -p $(BINDIR)
-	$(NVCC) $(ARCH) -O2 -std=c++17 -Iinclude -o $@ $< -L$(LIBDIR) -ldlaf_b200 -Xlinker -rpath -Xlinker '$$ORIGIN/../lib' -lcudart
+	$(NVCC) $(ARCH) -O2 -std=c++17 -Iinclude -Iinclude/dlafb_mpi_shim -o $@ $< -L$(LIBDIR) -ldlaf_b200 -Xlinker -rpath -Xlinker '$$ORIGIN/../lib' -lcudart
 
 oracle:
 	@mkdir -p oracle/_build

@@ -25,6 +25,7 @@ C_API = {
     "dlafb_mpi_comm_world": (c_vp, []),
     "dlafb_mpi_init": (c_int, [c_int, c_int, c_vp]),
     "dlafb_mpi_finalize": (c_int, []),
+    "dlafb_grid_create_from_comm": (c_int, [ctypes.POINTER(c_vp), c_vp, c_int, c_int, c_char]),
     "MPI_Comm_rank": (c_int, [c_vp, P_int]),
     "MPI_Comm_size": (c_int, [c_vp, P_int]),
 }

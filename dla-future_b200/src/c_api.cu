@@ -242,6 +242,14 @@ static dlafb_grid_t make_grid(MPI_Comm comm, int nprow, int npcol, char order) {
   return g;
 }
 
+// used by the C++ API (include/dlaf/communication/communicator_grid.h)
+int dlafb_grid_create_from_comm(dlafb_grid_t* grid, MPI_Comm comm, int nprow, int npcol, char order) {
+  if (!grid)
+    return -1;
+  *grid = make_grid(comm, nprow, npcol, order);
+  return 0;
+}
+
 int dlaf_create_grid(MPI_Comm comm, int nprow, int npcol, char order) noexcept {
   // contexts count down from INT_MAX so that they never collide with BLACS contexts (src/c_api/grid.cpp:28-40)
   int ctx = INT_MAX - (int)g_grids.size();
