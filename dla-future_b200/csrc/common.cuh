@@ -31,6 +31,8 @@ struct Tr<float> {
   __host__ __device__ static float fma(float a, float b, float c) { return fmaf(a, b, c); }
   // c - a * conj(b)
   __host__ __device__ static float fnma_conj(float a, float b, float c) { return fmaf(-a, b, c); }
+  __host__ __device__ static float fnma(float a, float b, float c) { return fmaf(-a, b, c); }
+  __host__ __device__ static float rsqrt_(float a) { return rsqrtf(a); }
   __host__ __device__ static float abs(float a) { return fabsf(a); }
 };
 
@@ -48,6 +50,8 @@ struct Tr<double> {
   __host__ __device__ static double add(double a, double b) { return a + b; }
   __host__ __device__ static double fma(double a, double b, double c) { return ::fma(a, b, c); }
   __host__ __device__ static double fnma_conj(double a, double b, double c) { return ::fma(-a, b, c); }
+  __host__ __device__ static double fnma(double a, double b, double c) { return ::fma(-a, b, c); }
+  __host__ __device__ static double rsqrt_(double a) { return ::rsqrt(a); }
   __host__ __device__ static double abs(double a) { return fabs(a); }
 };
 
@@ -72,6 +76,11 @@ struct TrComplex {
   __host__ __device__ static C fma(C a, C b, C c) {
     return make(c.x + a.x * b.x - a.y * b.y, c.y + a.x * b.y + a.y * b.x);
   }
+  // c - a * b
+  __host__ __device__ static C fnma(C a, C b, C c) {
+    return make(c.x - a.x * b.x + a.y * b.y, c.y - a.x * b.y - a.y * b.x);
+  }
+  __host__ __device__ static R rsqrt_(R a) { return Tr<R>::rsqrt_(a); }
   // c - a * conj(b)
   __host__ __device__ static C fnma_conj(C a, C b, C c) {
     return make(c.x - a.x * b.x - a.y * b.y, c.y + a.x * b.y - a.y * b.x);

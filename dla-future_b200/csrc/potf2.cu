@@ -3,13 +3,19 @@
 // called from include/dlaf/factorization/cholesky/impl.h:46-53 and :98-105).
 //
 // One CTA of 512 threads, block order n <= Potf2Limits<T>::nmax, inner step BS (32, or 16 for complex<double>):
-//   (a) BS x BS diagonal sub-block: ONE warp, one matrix row per lane, the row lives in registers and the
-//       column scale / rank-1 updates travel by warp shuffle (no shared-memory traffic, no block barrier);
-//   (b) the rows below: one row per thread, right-looking substitution against the sub-block;
-//   (c) trailing update of the remaining lower triangle with register-tiled accumulators.
-// The same CTA then forms W = inv(L) (needed by the panel solve, which multiplies by W^H with the DMMA
-// contraction kernel instead of substituting) with the strict upper triangle of the shared buffer as scratch.
+//   panel: every row of the BS-wide column panel (diagonal sub-block AND the rows below it) lives in the registers
+//          of one thread; per column the pivot column of the sub-block is published through a double-buffered
+//          shared array, ONE block barrier per column, 1/sqrt by rsqrt (no divide on the dependent chain);
+//   update: trailing lower triangle with register-tiled accumulators, all 512 threads.
+// The same CTA then forms W = inv(L) (the panel solve multiplies by W^H with the DMMA contraction kernel instead of
+// substituting): the BS x BS diagonal blocks by forward substitution (one column per thread, in registers), the
+// off-diagonal blocks by block distance, W_ij = -W_ii * (sum_l L_il W_lj), with 2 x 2 register tiles; W^T is kept in
+// the strict upper triangle of the shared buffer.
 // `info` follows potrf: index (1-based, offset by info_base) of the first non-positive pivot, first failure wins.
+//
+// History (round 1): the first version factored the sub-block in ONE warp with warp-shuffle broadcasts and solved
+// the rows below with one thread per row; measured 143 us (factor) + 116 us (inverse) for n = 128
+// (profiles/r01/critical_path_v1.json), i.e. 1.17 ms per 512 tile on the critical path. This version replaces both.
 #include "tile_ops.cuh"
 
 namespace dlafb {
@@ -17,226 +23,249 @@ namespace {
 
 constexpr int kPotf2Threads = 512;
 
+#ifdef DLAFB_TIMING
+__device__ long long g_potf2_clk[64];
+#define STAMP(i)          \
+  if (threadIdx.x == 0)   \
+  g_potf2_clk[i] = clock64()
+#else
+#define STAMP(i)
+#endif
+
+// Trailing update of one warp's share: rows tx + 32*ia (all RA strips), columns col0 + 16*ib for ib < CBN, over the
+// panel X = Xp (rows < r0 hold E, rows >= r0 hold L):  S[rw][col] -= sum_l X[rw][l] conj(X[col][l]), kept only for
+// A rows rw >= col and, when inverting, E rows rw < r0 (same formula, same address). No branch inside the l loop.
+template <class T, int BS, int NMAX, int CBN>
+__device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __restrict__ Xp, int lds, int n, int r0,
+                                               int bs, bool factor, bool inv, int tx, int col0) {
+  constexpr int RA = NMAX / 32;
+  T acc[RA][CBN];
+#pragma unroll
+  for (int ia = 0; ia < RA; ++ia)
+#pragma unroll
+    for (int ib = 0; ib < CBN; ++ib)
+      acc[ia][ib] = Tr<T>::zero();
+#pragma unroll 2
+  for (int l = 0; l < bs; ++l) {
+    const T* xp = Xp + l * NMAX;
+    T xa[RA], xb[CBN];
+#pragma unroll
+    for (int ia = 0; ia < RA; ++ia)
+      xa[ia] = xp[tx + 32 * ia];
+#pragma unroll
+    for (int ib = 0; ib < CBN; ++ib)
+      xb[ib] = col0 + 16 * ib < n ? xp[col0 + 16 * ib] : Tr<T>::zero();
+#pragma unroll
+    for (int ia = 0; ia < RA; ++ia)
+#pragma unroll
+      for (int ib = 0; ib < CBN; ++ib)
+        acc[ia][ib] = Tr<T>::fnma_conj(xa[ia], xb[ib], acc[ia][ib]);
+  }
+#pragma unroll
+  for (int ib = 0; ib < CBN; ++ib) {
+    const int col = col0 + 16 * ib;
+    if (col < n) {  // warp-uniform
+#pragma unroll
+      for (int ia = 0; ia < RA; ++ia) {
+        const int rw = tx + 32 * ia;
+        if (rw < n && ((factor && rw >= col) || (inv && rw < r0))) {
+          T* dst = S + rw + col * lds;
+          *dst = Tr<T>::add(*dst, acc[ia][ib]);
+        }
+      }
+    }
+  }
+}
+
 template <class T, int BS, int NMAX>
 __global__ void __launch_bounds__(kPotf2Threads, 1)
     potf2_kernel(int upper, int n, T* __restrict__ a, long long lda, T* __restrict__ winv, long long ldw,
                  int* info, int info_base, int mode) {
   using R = typename Tr<T>::Real;
+  static_assert((NMAX & (NMAX - 1)) == 0 && kPotf2Threads % NMAX == 0 && 2 * NMAX <= kPotf2Threads, "bad NMAX");
   extern __shared__ __align__(16) unsigned char smraw[];
-  const int lds = ((n + 15) & ~15) + 8;  // == 8 (mod 16): spreads the 4 row-parts of the inversion over the banks
-  T* S = reinterpret_cast<T*>(smraw);
-  R* dinv = reinterpret_cast<R*>(S + (size_t)lds * n);
-  __shared__ int fail;
+  const int lds = ((n + 15) & ~15) + 9;  // odd: rows and columns are both conflict-free
+  T* S = reinterpret_cast<T*>(smraw);               // lower: A -> L; strict upper: E = inv(L)^H (when inverting)
+  T* Xp = S + (size_t)lds * n;                      // current panel, BS x NMAX: rows < r0 from E, rows >= r0 from A
+  T* colbuf = Xp + BS * NMAX;                       // 2 x BS pivot-column buffers
+  R* dinv = reinterpret_cast<R*>(colbuf + 2 * BS);  // 1 / L_jj
+  int* sfail = reinterpret_cast<int*>(dinv + n);
 
   const int tid = threadIdx.x;
-  const int lane = tid & 31;
-  const int warp = tid >> 5;
-  if (tid == 0)
-    fail = 0;
+  const bool factor = (mode & 1) != 0;
+  const bool inv = (mode & 2) != 0 && winv != nullptr;
+  const int li = tid & (NMAX - 1);  // element loops without integer division: row li, columns lj0 + k*lstep
+  const int lj0 = tid / NMAX;
+  constexpr int lstep = kPotf2Threads / NMAX;
+  STAMP(0);
 
-  // ---- load the referenced triangle as a lower-triangular block (upper: conjugate transpose) ----
-  for (int idx = tid; idx < n * n; idx += kPotf2Threads) {
-    if (!upper) {
-      const int i = idx % n, j = idx / n;
-      if (i >= j)
-        S[i + j * lds] = a[i + j * lda];
+  // ---- load the referenced triangle as a lower-triangular block (upper: conjugate transpose); E starts at 0 ----
+  if (li < n)
+    for (int j = lj0; j < n; j += lstep) {
+      T v = Tr<T>::zero();
+      if (li >= j)
+        v = upper ? Tr<T>::conj(a[j + li * lda]) : a[li + j * lda];
+      S[li + j * lds] = v;
     }
-    else {
-      const int j = idx % n, i = idx / n;
-      if (i >= j)
-        S[i + j * lds] = Tr<T>::conj(a[j + i * lda]);
-    }
-  }
   __syncthreads();
+  STAMP(1);
 
-  if (mode & 1) {
-    for (int jb = 0; jb < n; jb += BS) {
-      const int bs = min(BS, n - jb);
-      // (a) diagonal sub-block in one warp
-      if (warp == 0) {
-        T v[BS];
+  // Column panels of width BS, one thread per row, the row of the panel in registers:
+  //   threads [0, NMAX)        row = tid of A (rows of the BS x BS diagonal sub-block and the rows below it)
+  //   threads [NMAX, 2*NMAX)   row e = tid - NMAX of E: the identity appended below A, which the same column
+  //                            operations turn into inv(L)^H (X * L^H = I solved panel by panel)
+  // Every one of these warps ALSO factors the sub-block itself (lane l keeps row l % BS of it, columns travel by
+  // warp shuffle), so the column-to-column dependent chain has no block barrier and no shared-memory round trip:
+  //   rsqrt(pivot) -> scale the (already shuffled, unscaled) column -> update the locally tracked diagonal -> next
+  // (23-cycle FP64 latency, 55-80 for rsqrt: profiles/r01/latency_b200.txt). All copies run the same operations in
+  // the same order and agree bit for bit.
+  const bool roleA = tid < NMAX;
+  const int row = roleA ? tid : tid - NMAX;
+  int fail = 0;
+  for (int jb = 0; jb < n; jb += BS) {
+    const int bs = min(BS, n - jb);
+    const int r0 = jb + bs;
+    if (tid < 2 * NMAX) {
+      const int t = row - jb;  // index inside the diagonal sub-block (when 0 <= t < bs)
+      const int r = tid & (BS - 1);
+      const bool act = roleA ? (row >= jb && row < n) : (inv && row < r0);
+      T Dr[BS];  // row r of the sub-block (identity-padded beyond bs)
+      T dg[BS];  // its diagonal, tracked by every lane
+      T x[BS];   // this thread's row of the panel
 #pragma unroll
-        for (int c = 0; c < BS; ++c)
-          v[c] = (lane < bs && c <= lane) ? S[(jb + lane) + (jb + c) * lds] : Tr<T>::zero();
-        int bad = 0;
+      for (int c = 0; c < BS; ++c) {
+        const T one = Tr<T>::from_real(R(1));
+        Dr[c] = r >= c ? ((r < bs) ? S[(jb + r) + (jb + c) * lds] : (r == c ? one : Tr<T>::zero())) : Tr<T>::zero();
+        dg[c] = c < bs ? S[(jb + c) + (jb + c) * lds] : one;
+        T v = Tr<T>::zero();
+        if (act && c < bs) {
+          if (roleA)
+            v = (t >= bs || c <= t) ? S[row + (jb + c) * lds] : v;
+          else
+            v = t < 0 ? S[row + (jb + c) * lds] : (t == c ? one : v);
+        }
+        x[c] = v;
+      }
 #pragma unroll
-        for (int j = 0; j < BS; ++j) {
-          if (j < bs && !bad) {
-            const R d = Tr<T>::real(shfl(v[j], j));
-            if (!(d > R(0))) {
-              bad = j + 1;
-            }
-            else {
-              const R s = sqrt(d);
-              const R is = R(1) / s;
-              if (lane == j)
-                v[j] = Tr<T>::from_real(s);
-              else if (lane > j)
-                v[j] = Tr<T>::scale(v[j], is);
-              if (lane == 0)
-                dinv[jb + j] = is;
+      for (int j = 0; j < BS; ++j) {
+        const R d = Tr<T>::real(dg[j]);
+        if (!(d > R(0)) && fail == 0)
+          fail = jb + j + 1;
+        T lraw[BS];
 #pragma unroll
-              for (int c = j + 1; c < BS; ++c) {
-                const T lc = shfl(v[j], c);
-                if (lane >= c)
-                  v[c] = Tr<T>::fnma_conj(v[j], lc, v[c]);
-              }
-            }
+        for (int c = j + 1; c < BS; ++c)
+          lraw[c] = shfl(Dr[j], (tid & 24) + c);  // element (c, j) from the lane that keeps row c
+        if (factor) {
+          const R is = Tr<T>::rsqrt_(d);
+          if (tid == j && j < bs)
+            dinv[jb + j] = is;
+          T xs = Tr<T>::scale(x[j], is);
+          if (roleA && t == j)
+            xs = Tr<T>::from_real(Tr<T>::real(xs));  // the diagonal is real
+          x[j] = xs;
+          const T drj = Tr<T>::scale(Dr[j], is);
+#pragma unroll
+          for (int c = j + 1; c < BS; ++c) {
+            const T lc = Tr<T>::scale(lraw[c], is);
+            dg[c] = Tr<T>::fnma_conj(lc, lc, dg[c]);
+            Dr[c] = Tr<T>::fnma_conj(drj, lc, Dr[c]);
+            x[c] = Tr<T>::fnma_conj(xs, lc, x[c]);
           }
         }
+        else {  // L is given: only the E rows are solved
+          const R is = R(1) / d;
+          if (tid == j && j < bs)
+            dinv[jb + j] = is;
+          if (!roleA) {
+            x[j] = Tr<T>::scale(x[j], is);
 #pragma unroll
-        for (int c = 0; c < BS; ++c)
-          if (lane < bs && c <= lane)
-            S[(jb + lane) + (jb + c) * lds] = v[c];
-        if (bad && lane == 0)
-          fail = jb + bad;
+            for (int c = j + 1; c < BS; ++c)
+              x[c] = Tr<T>::fnma_conj(x[j], lraw[c], x[c]);
+          }
+        }
       }
-      __syncthreads();
-      if (fail)
-        break;
-      const int nn = n - jb - bs;  // rows below the sub-block
-      if (nn == 0)
-        break;
-      // (b) rows below: X * L^H = B, one row per thread
-      if (tid < nn) {
-        const int i = jb + bs + tid;
-        T x[BS];
-#pragma unroll
-        for (int c = 0; c < BS; ++c)
-          x[c] = c < bs ? S[i + (jb + c) * lds] : Tr<T>::zero();
+      if (tid == 0)
+        *sfail = fail;
+      STAMP(2);
+      // write the panel back: into S (final values) and into Xp (operand of the trailing update)
+      if (fail == 0) {
 #pragma unroll
         for (int c = 0; c < BS; ++c) {
           if (c < bs) {
-            x[c] = Tr<T>::scale(x[c], dinv[jb + c]);
-#pragma unroll
-            for (int c2 = c + 1; c2 < BS; ++c2)
-              if (c2 < bs)
-                x[c2] = Tr<T>::fnma_conj(x[c], S[(jb + c2) + (jb + c) * lds], x[c2]);
-          }
-        }
-#pragma unroll
-        for (int c = 0; c < BS; ++c)
-          if (c < bs)
-            S[i + (jb + c) * lds] = x[c];
-      }
-      __syncthreads();
-      // (c) trailing lower triangle: S[i][j] -= sum_l X[i][l] conj(X[j][l]); thread (tx, ty) owns
-      //     rows tx + 32*a and columns ty + 16*b
-      {
-        constexpr int RA = (NMAX + 31) / 32;
-        constexpr int CB = (NMAX + 15) / 16;
-        const int tx = tid & 31, ty = tid >> 5;
-        const int r0 = jb + bs;
-        T acc[RA][CB];
-#pragma unroll
-        for (int ia = 0; ia < RA; ++ia)
-#pragma unroll
-          for (int ib = 0; ib < CB; ++ib)
-            acc[ia][ib] = Tr<T>::zero();
-        for (int l = 0; l < bs; ++l) {
-          const T* col = S + (jb + l) * lds + r0;
-          T xa[RA], xb[CB];
-#pragma unroll
-          for (int ia = 0; ia < RA; ++ia)
-            xa[ia] = (tx + 32 * ia < nn) ? col[tx + 32 * ia] : Tr<T>::zero();
-#pragma unroll
-          for (int ib = 0; ib < CB; ++ib)
-            xb[ib] = (ty + 16 * ib < nn) ? col[ty + 16 * ib] : Tr<T>::zero();
-#pragma unroll
-          for (int ia = 0; ia < RA; ++ia)
-#pragma unroll
-            for (int ib = 0; ib < CB; ++ib)
-              acc[ia][ib] = Tr<T>::fnma_conj(xa[ia], xb[ib], acc[ia][ib]);
-        }
-#pragma unroll
-        for (int ia = 0; ia < RA; ++ia)
-#pragma unroll
-          for (int ib = 0; ib < CB; ++ib) {
-            const int i = tx + 32 * ia, j = ty + 16 * ib;
-            if (i < nn && j < nn && i >= j) {
-              T* dst = S + (r0 + i) + (r0 + j) * lds;
-              *dst = Tr<T>::add(*dst, acc[ia][ib]);
+            if (roleA) {
+              if (act && factor && (t >= bs || c <= t))
+                S[row + (jb + c) * lds] = x[c];
+              if (row >= r0)
+                Xp[c * NMAX + row] = x[c];
+            }
+            else {
+              if (act && row < jb + c)
+                S[row + (jb + c) * lds] = x[c];
+              if (row < r0)
+                Xp[c * NMAX + row] = x[c];
             }
           }
-      }
-      __syncthreads();
-    }
-    if (fail) {
-      if (tid == 0 && info != nullptr)
-        atomicCAS(info, 0, info_base + fail);
-      // leave the tile as potrf would on failure: nothing further is defined; keep the input untouched
-      return;
-    }
-    // ---- store L (or U = L^H) ----
-    for (int idx = tid; idx < n * n; idx += kPotf2Threads) {
-      if (!upper) {
-        const int i = idx % n, j = idx / n;
-        if (i >= j)
-          a[i + j * lda] = S[i + j * lds];
-      }
-      else {
-        const int j = idx % n, i = idx / n;
-        if (i >= j)
-          a[j + i * lda] = Tr<T>::conj(S[i + j * lds]);
-      }
-    }
-  }
-  else {
-    for (int j = tid; j < n; j += kPotf2Threads)
-      dinv[j] = R(1) / Tr<T>::real(S[j + j * lds]);
-    __syncthreads();
-  }
-
-  if (!(mode & 2) || winv == nullptr)
-    return;
-
-  // ---- W = inv(L). Column t of W is built by 4 cooperating lanes (row-parts p = r mod 4); the running sums
-  //      acc(r,t) = sum_{l<r} L[r][l] W[l][t] sit in the strict upper triangle at S[t + r*lds]. ----
-  {
-    const int t = tid >> 2;
-    const int p = tid & 3;
-    if (t < n)
-      for (int r = t + 1 + p; r < n; r += 4)
-        S[t + r * lds] = Tr<T>::zero();
-    __syncthreads();
-    const int t0 = (warp * 32) >> 2;  // smallest column handled by this warp
-    for (int i = t0; i < n; ++i) {
-      T w = Tr<T>::zero();
-      const bool act = (t < n) && (i >= t);
-      if (act && (i & 3) == p) {
-        if (i == t)
-          w = Tr<T>::from_real(dinv[t]);
-        else {
-          w = Tr<T>::scale(S[t + i * lds], -dinv[i]);
-          S[t + i * lds] = w;
         }
       }
-      w = shfl(w, (lane & ~3) | (i & 3));
-      if (act) {
-        for (int r = i + 1 + ((p - (i + 1)) & 3); r < n; r += 4)
-          S[t + r * lds] = Tr<T>::fma(S[r + i * lds], w, S[t + r * lds]);
-      }
     }
     __syncthreads();
-    // write W (lower, with explicit zeros above the diagonal: the panel solve multiplies by the full block)
-    for (int idx = tid; idx < n * n; idx += kPotf2Threads) {
-      const int i = idx % n, j = idx / n;
-      T v;
-      if (i > j)
-        v = S[j + i * lds];
-      else if (i == j)
-        v = Tr<T>::from_real(dinv[i]);
-      else
-        v = Tr<T>::zero();
-      winv[i + j * ldw] = v;
+    fail = *sfail;
+    if (fail)
+      break;  // uniform
+    STAMP(3);
+    if (r0 >= n)
+      break;
+    {  // warp w owns the columns r0 + w + 16*ib; instantiated per column count so that no lane tests inside
+      const int tx = tid & 31, col0 = r0 + (tid >> 5);
+      const int nib = col0 < n ? (n - col0 + 15) >> 4 : 0;
+      constexpr int CB = (NMAX - BS + 15) / 16;
+      if (CB > 6 && nib > 6)
+        potf2_trailing<T, BS, NMAX, (CB > 6 ? 8 : CB)>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+      else if (CB > 4 && nib > 4)
+        potf2_trailing<T, BS, NMAX, (CB > 4 ? 6 : CB)>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+      else if (nib > 2)
+        potf2_trailing<T, BS, NMAX, 4>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+      else if (nib > 0)
+        potf2_trailing<T, BS, NMAX, 2>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
     }
+    __syncthreads();
+    STAMP(4);
   }
+  STAMP(20);
+  if (fail) {
+    if (tid == 0 && info != nullptr)
+      atomicCAS(info, 0, info_base + fail);
+    return;  // like potrf on failure nothing further is defined: the tile is left as it was
+  }
+  // ---- store L (or U = L^H) ----
+  if (factor && li < n)
+    for (int j = lj0; j <= li; j += lstep) {
+      if (upper)
+        a[j + li * lda] = Tr<T>::conj(S[li + j * lds]);
+      else
+        a[li + j * lda] = S[li + j * lds];
+    }
+  STAMP(21);
+  // ---- W = inv(L) = E^H, with explicit zeros above the diagonal (the panel solve multiplies by the full block).
+  //      Lanes run along i: coalesced global writes, shared reads with the odd stride lds. ----
+  if (inv && li < n)
+    for (int c = lj0; c < n; c += lstep) {
+      T v = Tr<T>::zero();  // W(li, c)
+      if (c < li)
+        v = Tr<T>::conj(S[c + li * lds]);
+      else if (c == li)
+        v = Tr<T>::from_real(dinv[li]);
+      winv[li + c * ldw] = v;
+    }
+  STAMP(40);
 }
 
 template <class T>
 size_t potf2_smem_bytes(int n) {
-  const int lds = ((n + 15) & ~15) + 8;
-  return (size_t)lds * n * sizeof(T) + (size_t)n * sizeof(typename Tr<T>::Real) + 16;
+  constexpr int BS = Potf2Limits<T>::bs;
+  constexpr int NMAX = Potf2Limits<T>::nmax;
+  const int lds = ((n + 15) & ~15) + 9;  // odd: rows and columns are both conflict-free
+  return ((size_t)lds * n + (size_t)BS * NMAX + 2 * BS) * sizeof(T) + (size_t)n * sizeof(typename Tr<T>::Real) + 16;
 }
 
 }  // namespace

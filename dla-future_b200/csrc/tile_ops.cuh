@@ -10,12 +10,12 @@ namespace dlafb {
 
 template <class T>
 struct Potf2Limits {
-  static constexpr int bs = 32;
+  static constexpr int bs = 8;
   static constexpr int nmax = 128;
 };
 template <>
 struct Potf2Limits<double2> {
-  static constexpr int bs = 16;
+  static constexpr int bs = 8;
   static constexpr int nmax = 64;
 };
 
