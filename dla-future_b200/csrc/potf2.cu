@@ -32,19 +32,34 @@ __device__ long long g_potf2_clk[64];
 #define STAMP(i)
 #endif
 
+template <class T, int NMAX>
+struct Potf2Smem {
+  using R = typename Tr<T>::Real;
+  static constexpr int lds = NMAX + 9;    // odd: walking along a row or along a column is bank-conflict free
+  static constexpr int ncol = NMAX + 1;   // one dummy column absorbs the out-of-range lanes of the trailing update
+  static constexpr size_t bytes(int bs) {
+    return ((size_t)lds * ncol + (size_t)bs * NMAX) * sizeof(T) + (size_t)NMAX * sizeof(R) + 16;
+  }
+};
+
 // Trailing update of one warp's share: rows tx + 32*ia (all RA strips), columns col0 + 16*ib for ib < CBN, over the
 // panel X = Xp (rows < r0 hold E, rows >= r0 hold L):  S[rw][col] -= sum_l X[rw][l] conj(X[col][l]), kept only for
-// A rows rw >= col and, when inverting, E rows rw < r0 (same formula, same address). No branch inside the l loop.
+// A rows rw >= col and, when inverting, E rows rw < r0 (same formula, same address). Straight-line code: no branch
+// in the l loop, and the read-modify-write adds a selected zero instead of branching per element.
 template <class T, int BS, int NMAX, int CBN>
-__device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __restrict__ Xp, int lds, int n, int r0,
-                                               int bs, bool factor, bool inv, int tx, int col0) {
+__device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __restrict__ Xp, int n, int r0, int bs,
+                                               bool factor, bool inv, int tx, int col0) {
   constexpr int RA = NMAX / 32;
+  constexpr int LDS = Potf2Smem<T, NMAX>::lds;
   T acc[RA][CBN];
+  int cidx[CBN];
 #pragma unroll
-  for (int ia = 0; ia < RA; ++ia)
+  for (int ib = 0; ib < CBN; ++ib) {
+    cidx[ib] = min(col0 + 16 * ib, NMAX - 1);
 #pragma unroll
-    for (int ib = 0; ib < CBN; ++ib)
+    for (int ia = 0; ia < RA; ++ia)
       acc[ia][ib] = Tr<T>::zero();
+  }
 #pragma unroll 2
   for (int l = 0; l < bs; ++l) {
     const T* xp = Xp + l * NMAX;
@@ -54,7 +69,7 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
       xa[ia] = xp[tx + 32 * ia];
 #pragma unroll
     for (int ib = 0; ib < CBN; ++ib)
-      xb[ib] = col0 + 16 * ib < n ? xp[col0 + 16 * ib] : Tr<T>::zero();
+      xb[ib] = xp[cidx[ib]];
 #pragma unroll
     for (int ia = 0; ia < RA; ++ia)
 #pragma unroll
@@ -64,49 +79,47 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
 #pragma unroll
   for (int ib = 0; ib < CBN; ++ib) {
     const int col = col0 + 16 * ib;
-    if (col < n) {  // warp-uniform
+    const bool colok = col < n;
+    T* dcol = S + (colok ? col : NMAX) * LDS;
 #pragma unroll
-      for (int ia = 0; ia < RA; ++ia) {
-        const int rw = tx + 32 * ia;
-        if (rw < n && ((factor && rw >= col) || (inv && rw < r0))) {
-          T* dst = S + rw + col * lds;
-          *dst = Tr<T>::add(*dst, acc[ia][ib]);
-        }
-      }
+    for (int ia = 0; ia < RA; ++ia) {
+      const int rw = tx + 32 * ia;
+      const bool keep = colok && rw < n && ((factor && rw >= col) || (inv && rw < r0));
+      dcol[rw] = Tr<T>::add(dcol[rw], keep ? acc[ia][ib] : Tr<T>::zero());
     }
   }
 }
 
-template <class T, int BS, int NMAX>
+template <class T, int BS, int NMAX, bool FACTOR>
 __global__ void __launch_bounds__(kPotf2Threads, 1)
     potf2_kernel(int upper, int n, T* __restrict__ a, long long lda, T* __restrict__ winv, long long ldw,
-                 int* info, int info_base, int mode) {
+                 int* info, int info_base) {
   using R = typename Tr<T>::Real;
+  using Sm = Potf2Smem<T, NMAX>;
   static_assert((NMAX & (NMAX - 1)) == 0 && kPotf2Threads % NMAX == 0 && 2 * NMAX <= kPotf2Threads, "bad NMAX");
+  static_assert(BS == 8, "lane l keeps row l % 8 of the sub-block");
   extern __shared__ __align__(16) unsigned char smraw[];
-  const int lds = ((n + 15) & ~15) + 9;  // odd: rows and columns are both conflict-free
-  T* S = reinterpret_cast<T*>(smraw);               // lower: A -> L; strict upper: E = inv(L)^H (when inverting)
-  T* Xp = S + (size_t)lds * n;                      // current panel, BS x NMAX: rows < r0 from E, rows >= r0 from A
-  T* colbuf = Xp + BS * NMAX;                       // 2 x BS pivot-column buffers
-  R* dinv = reinterpret_cast<R*>(colbuf + 2 * BS);  // 1 / L_jj
-  int* sfail = reinterpret_cast<int*>(dinv + n);
+  constexpr int LDS = Sm::lds;
+  T* S = reinterpret_cast<T*>(smraw);             // lower: A -> L; strict upper: E = inv(L)^H (when inverting)
+  T* Xp = S + (size_t)LDS * Sm::ncol;             // current panel, BS x NMAX: rows < r0 from E, rows >= r0 from A
+  R* dinv = reinterpret_cast<R*>(Xp + BS * NMAX);  // 1 / L_jj
+  int* sfail = reinterpret_cast<int*>(dinv + NMAX);
 
   const int tid = threadIdx.x;
-  const bool factor = (mode & 1) != 0;
-  const bool inv = (mode & 2) != 0 && winv != nullptr;
+  const bool inv = winv != nullptr;
   const int li = tid & (NMAX - 1);  // element loops without integer division: row li, columns lj0 + k*lstep
   const int lj0 = tid / NMAX;
   constexpr int lstep = kPotf2Threads / NMAX;
+  const T one = Tr<T>::from_real(R(1));
   STAMP(0);
 
-  // ---- load the referenced triangle as a lower-triangular block (upper: conjugate transpose); E starts at 0 ----
-  if (li < n)
-    for (int j = lj0; j < n; j += lstep) {
-      T v = Tr<T>::zero();
-      if (li >= j)
-        v = upper ? Tr<T>::conj(a[j + li * lda]) : a[li + j * lda];
-      S[li + j * lds] = v;
-    }
+  // ---- load the referenced triangle as a lower-triangular block (upper: conjugate transpose); zero elsewhere ----
+  for (int j = lj0; j < n; j += lstep) {
+    T v = Tr<T>::zero();
+    if (li < n && li >= j)
+      v = upper ? Tr<T>::conj(a[j + li * lda]) : a[li + j * lda];
+    S[li + j * LDS] = v;
+  }
   __syncthreads();
   STAMP(1);
 
@@ -118,7 +131,8 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
   // warp shuffle), so the column-to-column dependent chain has no block barrier and no shared-memory round trip:
   //   rsqrt(pivot) -> scale the (already shuffled, unscaled) column -> update the locally tracked diagonal -> next
   // (23-cycle FP64 latency, 55-80 for rsqrt: profiles/r01/latency_b200.txt). All copies run the same operations in
-  // the same order and agree bit for bit.
+  // the same order and agree bit for bit. Loads and stores are select/predicate only: divergent branches cost more
+  // than the arithmetic here.
   const bool roleA = tid < NMAX;
   const int row = roleA ? tid : tid - NMAX;
   int fail = 0;
@@ -126,6 +140,7 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
     const int bs = min(BS, n - jb);
     const int r0 = jb + bs;
     if (tid < 2 * NMAX) {
+      T* Sp = S + jb * LDS;    // the panel's columns
       const int t = row - jb;  // index inside the diagonal sub-block (when 0 <= t < bs)
       const int r = tid & (BS - 1);
       const bool act = roleA ? (row >= jb && row < n) : (inv && row < r0);
@@ -134,28 +149,24 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
       T x[BS];   // this thread's row of the panel
 #pragma unroll
       for (int c = 0; c < BS; ++c) {
-        const T one = Tr<T>::from_real(R(1));
-        Dr[c] = r >= c ? ((r < bs) ? S[(jb + r) + (jb + c) * lds] : (r == c ? one : Tr<T>::zero())) : Tr<T>::zero();
-        dg[c] = c < bs ? S[(jb + c) + (jb + c) * lds] : one;
-        T v = Tr<T>::zero();
-        if (act && c < bs) {
-          if (roleA)
-            v = (t >= bs || c <= t) ? S[row + (jb + c) * lds] : v;
-          else
-            v = t < 0 ? S[row + (jb + c) * lds] : (t == c ? one : v);
-        }
-        x[c] = v;
+        const T dv = Sp[(jb + r) + c * LDS];
+        const T gv = Sp[(jb + c) + c * LDS];
+        const T xv = Sp[row + c * LDS];
+        Dr[c] = (r >= c && r < bs) ? dv : (r == c ? one : Tr<T>::zero());
+        dg[c] = c < bs ? gv : one;
+        const bool in = act && c < bs;
+        const bool keep = roleA ? (in && (t >= bs || c <= t)) : (in && t < 0);
+        x[c] = keep ? xv : ((!roleA && in && t == c) ? one : Tr<T>::zero());
       }
 #pragma unroll
       for (int j = 0; j < BS; ++j) {
         const R d = Tr<T>::real(dg[j]);
-        if (!(d > R(0)) && fail == 0)
-          fail = jb + j + 1;
+        fail = (!(d > R(0)) && fail == 0) ? jb + j + 1 : fail;
         T lraw[BS];
 #pragma unroll
         for (int c = j + 1; c < BS; ++c)
           lraw[c] = shfl(Dr[j], (tid & 24) + c);  // element (c, j) from the lane that keeps row c
-        if (factor) {
+        if (FACTOR) {
           const R is = Tr<T>::rsqrt_(d);
           if (tid == j && j < bs)
             dinv[jb + j] = is;
@@ -172,47 +183,37 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
             x[c] = Tr<T>::fnma_conj(xs, lc, x[c]);
           }
         }
-        else {  // L is given: only the E rows are solved
+        else {  // L is given: only the E rows are solved (A rows pass through unchanged)
           const R is = R(1) / d;
           if (tid == j && j < bs)
             dinv[jb + j] = is;
-          if (!roleA) {
-            x[j] = Tr<T>::scale(x[j], is);
+          const T xs = roleA ? x[j] : Tr<T>::scale(x[j], is);
+          x[j] = xs;
 #pragma unroll
-            for (int c = j + 1; c < BS; ++c)
-              x[c] = Tr<T>::fnma_conj(x[j], lraw[c], x[c]);
-          }
+          for (int c = j + 1; c < BS; ++c)
+            x[c] = roleA ? x[c] : Tr<T>::fnma_conj(xs, lraw[c], x[c]);
         }
       }
       if (tid == 0)
         *sfail = fail;
-      STAMP(2);
+      STAMP(4 + 3 * (jb / BS));
       // write the panel back: into S (final values) and into Xp (operand of the trailing update)
-      if (fail == 0) {
 #pragma unroll
-        for (int c = 0; c < BS; ++c) {
-          if (c < bs) {
-            if (roleA) {
-              if (act && factor && (t >= bs || c <= t))
-                S[row + (jb + c) * lds] = x[c];
-              if (row >= r0)
-                Xp[c * NMAX + row] = x[c];
-            }
-            else {
-              if (act && row < jb + c)
-                S[row + (jb + c) * lds] = x[c];
-              if (row < r0)
-                Xp[c * NMAX + row] = x[c];
-            }
-          }
-        }
+      for (int c = 0; c < BS; ++c) {
+        const bool in = c < bs;
+        const bool ps = in && act && (roleA ? (FACTOR && (t >= bs || c <= t)) : (row < jb + c));
+        const bool px = in && (roleA ? row >= r0 : row < r0);
+        if (ps)
+          Sp[row + c * LDS] = x[c];
+        if (px)
+          Xp[c * NMAX + row] = x[c];
       }
     }
     __syncthreads();
     fail = *sfail;
     if (fail)
       break;  // uniform
-    STAMP(3);
+    STAMP(5 + 3 * (jb / BS));
     if (r0 >= n)
       break;
     {  // warp w owns the columns r0 + w + 16*ib; instantiated per column count so that no lane tests inside
@@ -220,52 +221,44 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
       const int nib = col0 < n ? (n - col0 + 15) >> 4 : 0;
       constexpr int CB = (NMAX - BS + 15) / 16;
       if (CB > 6 && nib > 6)
-        potf2_trailing<T, BS, NMAX, (CB > 6 ? 8 : CB)>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, (CB > 6 ? 8 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
       else if (CB > 4 && nib > 4)
-        potf2_trailing<T, BS, NMAX, (CB > 4 ? 6 : CB)>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, (CB > 4 ? 6 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
       else if (nib > 2)
-        potf2_trailing<T, BS, NMAX, 4>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, 4>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
       else if (nib > 0)
-        potf2_trailing<T, BS, NMAX, 2>(S, Xp, lds, n, r0, bs, factor, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, 2>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
     }
     __syncthreads();
-    STAMP(4);
+    STAMP(6 + 3 * (jb / BS));
   }
-  STAMP(20);
+  STAMP(60);
   if (fail) {
     if (tid == 0 && info != nullptr)
       atomicCAS(info, 0, info_base + fail);
     return;  // like potrf on failure nothing further is defined: the tile is left as it was
   }
   // ---- store L (or U = L^H) ----
-  if (factor && li < n)
+  if (FACTOR && li < n)
     for (int j = lj0; j <= li; j += lstep) {
       if (upper)
-        a[j + li * lda] = Tr<T>::conj(S[li + j * lds]);
+        a[j + li * lda] = Tr<T>::conj(S[li + j * LDS]);
       else
-        a[li + j * lda] = S[li + j * lds];
+        a[li + j * lda] = S[li + j * LDS];
     }
-  STAMP(21);
+  STAMP(61);
   // ---- W = inv(L) = E^H, with explicit zeros above the diagonal (the panel solve multiplies by the full block).
-  //      Lanes run along i: coalesced global writes, shared reads with the odd stride lds. ----
+  //      Lanes run along i: coalesced global writes, shared reads with the odd stride LDS. ----
   if (inv && li < n)
     for (int c = lj0; c < n; c += lstep) {
       T v = Tr<T>::zero();  // W(li, c)
       if (c < li)
-        v = Tr<T>::conj(S[c + li * lds]);
+        v = Tr<T>::conj(S[c + li * LDS]);
       else if (c == li)
         v = Tr<T>::from_real(dinv[li]);
       winv[li + c * ldw] = v;
     }
-  STAMP(40);
-}
-
-template <class T>
-size_t potf2_smem_bytes(int n) {
-  constexpr int BS = Potf2Limits<T>::bs;
-  constexpr int NMAX = Potf2Limits<T>::nmax;
-  const int lds = ((n + 15) & ~15) + 9;  // odd: rows and columns are both conflict-free
-  return ((size_t)lds * n + (size_t)BS * NMAX + 2 * BS) * sizeof(T) + (size_t)n * sizeof(typename Tr<T>::Real) + 16;
+  STAMP(62);
 }
 
 }  // namespace
@@ -275,17 +268,25 @@ cudaError_t launch_potf2(cudaStream_t stream, char uplo, int n, T* a, long long 
                          int* info, int info_base, int mode) {
   constexpr int BS = Potf2Limits<T>::bs;
   constexpr int NMAX = Potf2Limits<T>::nmax;
+  constexpr size_t smem = Potf2Smem<T, NMAX>::bytes(BS);
   if (n <= 0)
     return cudaSuccess;
   if (n > NMAX)
     return cudaErrorInvalidValue;
-  auto kern = potf2_kernel<T, BS, NMAX>;
-  static cudaError_t attr =
-      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)potf2_smem_bytes<T>(NMAX));
-  if (attr != cudaSuccess)
-    return attr;
-  kern<<<1, kPotf2Threads, potf2_smem_bytes<T>(n), stream>>>(uplo == 'U' || uplo == 'u', n, a, lda, winv, ldw, info,
-                                                             info_base, mode);
+  auto kern_f = potf2_kernel<T, BS, NMAX, true>;
+  auto kern_i = potf2_kernel<T, BS, NMAX, false>;
+  static cudaError_t attr_f = cudaFuncSetAttribute(kern_f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  static cudaError_t attr_i = cudaFuncSetAttribute(kern_i, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (attr_f != cudaSuccess || attr_i != cudaSuccess)
+    return attr_f != cudaSuccess ? attr_f : attr_i;
+  T* w = (mode & 2) ? winv : nullptr;
+  const int up = uplo == 'U' || uplo == 'u';
+  if (mode & 1)
+    kern_f<<<1, kPotf2Threads, smem, stream>>>(up, n, a, lda, w, ldw, info, info_base);
+  else if (w != nullptr)
+    kern_i<<<1, kPotf2Threads, smem, stream>>>(up, n, a, lda, w, ldw, info, info_base);
+  else
+    return cudaSuccess;
   ++g_launches;
   return cudaGetLastError();
 }

@@ -75,7 +75,7 @@ int main() {
   long long clk[64];
   cudaMemcpyFromSymbol(clk, g_potf2_clk, sizeof(clk));
   printf(", \"clk\": [");
-  for (int i = 0; i < 41; ++i) printf("%lld%s", clk[i] ? clk[i] - clk[0] : -1, i < 40 ? ", " : "]");
+  for (int i = 0; i < 63; ++i) printf("%lld%s", clk[i] ? clk[i] - clk[0] : -1, i < 62 ? ", " : "]");
 #endif
   int hinfo = -1;
   cudaMemcpy(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost);
