@@ -61,20 +61,27 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                : "d"(a), "d"(b));
 }
 
+// BM x BN block of C per CTA; 8 warps as 2 (rows) x 4 (cols), each owning (BM/2) x (BN/4) of it as F x G DMMA
+// fragments. 128 x 128 is the throughput shape; the smaller ones exist for the launches on the critical path of the
+// factorization (few CTAs, each a serial chain of K/16 slices at 128 flop/clk/SM).
+template <int BM, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
     gemm_nt_dmma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                         const GemmParams p) {
   // ---- which block of C ----
+  constexpr int F = BM / 16, G = BN / 32;  // 8-row / 8-column fragments per warp
+  constexpr int kABytes = BM * kBK * 8, kBBytes = BN * kBK * 8, kStageB = kABytes + kBBytes;
+  static_assert(F >= 2 && G >= 2 && F % 2 == 0 && G % 2 == 0, "a warp owns whole 16-row groups of both operands");
   int trow, tcol, row0, col0, lower, m_lim = p.m_total, n_lim = p.n_total;
   int b_from_a = 0, b_row_a = 0;  // LIST mode, diagonal tile: both operands come from the row panel (HERK)
   if (p.list != nullptr) {
-    const int nsub = p.sub * p.sub;
+    const int sub_m = p.tile / BM, nsub = sub_m * (p.tile / BN);
     const int item = blockIdx.x / nsub;
     const int s = blockIdx.x - item * nsub;
     const int2 it = p.list[item];
     lower = it.y < 0;
-    trow = (s % p.sub) * kBM;
-    tcol = (s / p.sub) * kBN;
+    trow = (s % sub_m) * BM;
+    tcol = (s / sub_m) * BN;
     row0 = it.x + trow;
     col0 = (it.y & 0x7fffffff) + tcol;
     b_from_a = lower;
@@ -84,19 +91,19 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   }
   else {
     lower = p.lower;
-    trow = blockIdx.x * kBM;
-    tcol = blockIdx.y * kBN;
+    trow = blockIdx.x * BM;
+    tcol = blockIdx.y * BN;
     row0 = p.rect_row0 + trow;
     col0 = p.rect_col0 + tcol;
   }
   if (row0 >= m_lim || col0 >= n_lim)
     return;
-  if (lower && trow + kBM - 1 < tcol)
+  if (lower && trow + BM - 1 < tcol)
     return;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_full = base + kStages * kStageBytes;
+  const uint32_t bar_full = base + kStages * kStageB;
   const uint32_t bar_empty = bar_full + 8 * kStages;
 
   const int warp = threadIdx.x >> 5;
@@ -115,8 +122,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 
   // ---- pull this block of C into L2 while the contraction runs (the epilogue reads it) ----
   if (p.beta != 0.0) {
-    const int rows = min(kBM, m_lim - row0);
-    const int cols = min(kBN, n_lim - col0);
+    const int rows = min(BM, m_lim - row0);
+    const int cols = min(BN, n_lim - col0);
     const int segs = (rows + 15) >> 4;  // 128-byte lines per column
     for (int i = threadIdx.x; i < cols * segs; i += kGemmThreads) {
       const int c = i / segs, sgm = i - c * segs;
@@ -137,9 +144,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     const uint32_t ph = (kt / kStages) & 1;
     mbar_wait(bar_empty + 8 * s, ph ^ 1);
     const uint32_t full = bar_full + 8 * s;
-    mbar_expect_tx(full, kStageBytes);
-    const uint32_t sa = base + s * kStageBytes;
-    const uint32_t sb = sa + kOperandStageBytes;
+    mbar_expect_tx(full, kStageB);
+    const uint32_t sa = base + s * kStageB;
+    const uint32_t sb = sa + kABytes;
     const int ka = p.a_col0 + kt * kBK;
     const int kb = b_col0 + kt * kBK;
     if (p.nbox_a == 1)
@@ -147,31 +154,31 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     else if (p.nbox_a == 4)
       tma_load_4d(sa, &map_a, 0, ka, (a_row % p.tile) >> 4, a_row / p.tile, full);
     else
-      for (int g = 0; g < 8; ++g)
+      for (int g = 0; g < BM / 16; ++g)
         tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
     if (nbox_b == 1)
       tma_load_3d(sb, mb, 0, kb, b_row >> 4, full);
     else if (nbox_b == 4)
       tma_load_4d(sb, mb, 0, kb, (b_row % p.tile) >> 4, b_row / p.tile, full);
     else
-      for (int g = 0; g < 8; ++g)
+      for (int g = 0; g < BN / 16; ++g)
         tma_load_2d(sb + g * kGroupBytes, mb, b_row + 16 * g, kb, full);
   };
   if (producer)
     for (int kt = 0; kt < kPrefetch && kt < nk; ++kt)
       issue(kt);
 
-  // ---- DMMA: 8 warps as 2 (rows) x 4 (cols); each owns a 64 x 32 block of C ----
+  // ---- DMMA: 8 warps as 2 (rows) x 4 (cols); each owns a (BM/2) x (BN/4) block of C ----
   const int wm = warp & 1;
   const int wn = warp >> 1;
   const int r = lane >> 2;   // fragment row (A) / column (B)
   const int kk = lane & 3;   // fragment k index; MMA step s4 uses k-columns 8*(s4/2) + 2*kk + (s4&1)
 
-  double acc[8][4][2];
+  double acc[F][G][2];
 #pragma unroll
-  for (int f = 0; f < 8; ++f)
+  for (int f = 0; f < F; ++f)
 #pragma unroll
-    for (int g = 0; g < 4; ++g)
+    for (int g = 0; g < G; ++g)
       acc[f][g][0] = acc[f][g][1] = 0.0;
 
   // Swizzle<3,4,3> of the 128B rows: 16-byte chunk index ^= (k-column & 7). With the k permutation above
@@ -182,8 +189,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 #pragma unroll
     for (int sb = 0; sb < 2; ++sb)
       xo[fb][sb] = (((uint32_t)((fb << 2) | (r >> 1)) ^ (uint32_t)((kk << 1) | sb)) << 4) + ((r & 1) << 3);
-  const uint32_t a_thr = (wm * 4) * kGroupBytes + (2 * kk) * 128;
-  const uint32_t b_thr = kOperandStageBytes + (wn * 2) * kGroupBytes + (2 * kk) * 128;
+  const uint32_t a_thr = (wm * (F / 2)) * kGroupBytes + (2 * kk) * 128;
+  const uint32_t b_thr = kABytes + (wn * (G / 2)) * kGroupBytes + (2 * kk) * 128;
 
   for (int kt = 0; kt < nk; ++kt) {
     // refill the stage freed two slices ago: its empty barrier is (almost always) already complete
@@ -192,21 +199,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     const int s = kt % kStages;
     const uint32_t ph = (kt / kStages) & 1;
     mbar_wait(bar_full + 8 * s, ph);
-    const uint32_t st = base + s * kStageBytes;
+    const uint32_t st = base + s * kStageB;
 #pragma unroll
     for (int s4 = 0; s4 < 4; ++s4) {
       const uint32_t koff = (8 * (s4 >> 1) + (s4 & 1)) * 128;
-      double a[8], b[4];
+      double a[F], b[G];
 #pragma unroll
-      for (int f = 0; f < 8; ++f)
+      for (int f = 0; f < F; ++f)
         a[f] = lds_f64(st + a_thr + (f >> 1) * kGroupBytes + koff + xo[f & 1][s4 & 1]);
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
+      for (int g = 0; g < G; ++g)
         b[g] = lds_f64(st + b_thr + (g >> 1) * kGroupBytes + koff + xo[g & 1][s4 & 1]);
 #pragma unroll
-      for (int f = 0; f < 8; ++f)
+      for (int f = 0; f < F; ++f)
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
+        for (int g = 0; g < G; ++g)
           dmma884(acc[f][g][0], acc[f][g][1], a[f], b[g]);
     }
     __syncwarp();
@@ -216,57 +223,57 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 
   // ---- epilogue: C <- beta*C + alpha*acc, clipped and (optionally) restricted to the lower triangle ----
   const double alpha = p.alpha, beta = p.beta;
-  const bool full_block = !lower || (trow >= tcol + kBN - 1);
-  if (full_block && row0 + kBM <= m_lim && col0 + kBN <= n_lim) {
+  const bool full_block = !lower || (trow >= tcol + BN - 1);
+  if (full_block && row0 + BM <= m_lim && col0 + BN <= n_lim) {
     // interior block: no predicates; the 16 loads of column group g+1 are in flight while group g is stored
-    double* cb = p.C + (long long)(col0 + wn * 32 + 2 * kk) * p.ldc + (row0 + wm * 64 + r);
+    double* cb = p.C + (long long)(col0 + wn * (BN / 4) + 2 * kk) * p.ldc + (row0 + wm * (BM / 2) + r);
     const long long ldc = p.ldc;
     if (beta != 0.0) {
-      double cv[2][2][8];
+      double cv[2][2][F];
 #pragma unroll
       for (int e = 0; e < 2; ++e)
 #pragma unroll
-        for (int f = 0; f < 8; ++f)
+        for (int f = 0; f < F; ++f)
           cv[0][e][f] = __ldcg(cb + e * ldc + f * 8);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        if (g + 1 < 4) {
+      for (int g = 0; g < G; ++g) {
+        if (g + 1 < G) {
 #pragma unroll
           for (int e = 0; e < 2; ++e)
 #pragma unroll
-            for (int f = 0; f < 8; ++f)
+            for (int f = 0; f < F; ++f)
               cv[(g + 1) & 1][e][f] = __ldcg(cb + ((g + 1) * 8 + e) * ldc + f * 8);
         }
 #pragma unroll
         for (int e = 0; e < 2; ++e)
 #pragma unroll
-          for (int f = 0; f < 8; ++f)
+          for (int f = 0; f < F; ++f)
             __stcg(cb + (g * 8 + e) * ldc + f * 8, fma(beta, cv[g & 1][e][f], alpha * acc[f][g][e]));
       }
     }
     else {
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
+      for (int g = 0; g < G; ++g)
 #pragma unroll
         for (int e = 0; e < 2; ++e)
 #pragma unroll
-          for (int f = 0; f < 8; ++f)
+          for (int f = 0; f < F; ++f)
             __stcg(cb + (g * 8 + e) * ldc + f * 8, alpha * acc[f][g][e]);
     }
     return;
   }
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
+  for (int g = 0; g < G; ++g) {
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
-      const int cl = wn * 32 + g * 8 + 2 * kk + e;  // column inside the CTA block
+      const int cl = wn * (BN / 4) + g * 8 + 2 * kk + e;  // column inside the CTA block
       const int c = col0 + cl;
       if (c >= n_lim)
         continue;
       double* colp = p.C + (long long)c * p.ldc;
 #pragma unroll
-      for (int f = 0; f < 8; ++f) {
-        const int rl = wm * 64 + f * 8 + r;
+      for (int f = 0; f < F; ++f) {
+        const int rl = wm * (BM / 2) + f * 8 + r;
         const int rr = row0 + rl;
         if (rr >= m_lim)
           continue;
@@ -300,7 +307,8 @@ EncodeTiledFn encode_fn() {
 }  // namespace
 
 int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
-                     int kind) {
+                     int kind, int box_rows) {
+  const cuuint32_t groups = (cuuint32_t)(box_rows / 16);
   EncodeTiledFn enc = encode_fn();
   if (!enc)
     return -1;
@@ -310,7 +318,7 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
   if (kind == 3) {
     cuuint64_t dims[3] = {16, (cuuint64_t)cols, (cuuint64_t)((rows + 15) / 16)};
     cuuint64_t strides[2] = {(cuuint64_t)ld * 8, 128};
-    cuuint32_t box[3] = {16, (cuuint32_t)kBK, 8};
+    cuuint32_t box[3] = {16, (cuuint32_t)kBK, groups};
     cuuint32_t es[3] = {1, 1, 1};
     r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base), dims, strides, box, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -321,7 +329,7 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
     const cuuint64_t nb = (cuuint64_t)ld;
     cuuint64_t dims[4] = {16, nb, nb / 16, (cuuint64_t)(rows / ld)};
     cuuint64_t strides[3] = {nb * 8, 128, nb * nb * 8};
-    cuuint32_t box[4] = {16, (cuuint32_t)kBK, 8, 1};
+    cuuint32_t box[4] = {16, (cuuint32_t)kBK, groups, 1};
     cuuint32_t es[4] = {1, 1, 1, 1};
     r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<double*>(base), dims, strides, box, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -339,17 +347,34 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
   return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
-cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
-                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y) {
-  static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 kGemmSmemBytes);
+namespace {
+template <int BM, int BN>
+cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& p,
+                         unsigned nx, unsigned ny) {
+  constexpr int smem = gemm_smem_bytes(BM, BN);
+  static cudaError_t attr =
+      cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (attr != cudaSuccess)
     return attr;
-  if (nblocks_x == 0 || nblocks_y == 0)
-    return cudaSuccess;
-  gemm_nt_dmma_kernel<<<dim3(nblocks_x, nblocks_y), kGemmThreads, kGemmSmemBytes, stream>>>(map_a, map_b, p);
+  gemm_nt_dmma_kernel<BM, BN><<<dim3(nx, ny), kGemmThreads, smem, stream>>>(map_a, map_b, p);
   ++g_launches;
   return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
+                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y, GemmShape shape) {
+  if (nblocks_x == 0 || nblocks_y == 0)
+    return cudaSuccess;
+  switch (shape) {
+    case GemmShape::k128x128:
+      return launch_shape<128, 128>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+    case GemmShape::k64x64:
+      return launch_shape<64, 64>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+    case GemmShape::k32x128:
+      return launch_shape<32, 128>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+  }
+  return cudaErrorInvalidValue;
 }
 
 }  // namespace dlafb

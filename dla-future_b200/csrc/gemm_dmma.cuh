@@ -24,6 +24,20 @@ constexpr int kGemmSmemBytes = kStages * kStageBytes + 2 * kStages * 8 + 1024;  
 constexpr int kGemmThreads = 256;  // 8 DMMA warps; lane 0 of warp 0 also issues the TMA loads
 constexpr int kPrefetch = kStages - 2;  // slices in flight ahead of the math (refills the stage freed two slices ago)
 
+// Block of C per CTA. 128 x 128 is the throughput shape (88 % of the DMMA peak); one CTA needs 2.1 us per K-slice of
+// 16 whatever the shape's area ratio, so the launches on the critical path (few blocks, K = 128..512) use the small
+// shapes: 4x (64 x 64) or 4x (32 x 128, the in-place panel solve needs all N columns in one CTA) more CTAs.
+enum class GemmShape : int { k128x128 = 0, k64x64 = 1, k32x128 = 2 };
+constexpr int shape_bm(GemmShape s) {
+  return s == GemmShape::k128x128 ? 128 : s == GemmShape::k64x64 ? 64 : 32;
+}
+constexpr int shape_bn(GemmShape s) {
+  return s == GemmShape::k64x64 ? 64 : 128;
+}
+constexpr int gemm_smem_bytes(int bm, int bn) {
+  return kStages * (bm + bn) * kBK * 8 + 2 * kStages * 8 + 1024;  // stages + barriers + align slack
+}
+
 struct GemmParams {
   double* C;
   long long ldc;
@@ -33,10 +47,9 @@ struct GemmParams {
   int a_row_off, b_row_off;  // A row = C row + a_row_off, B row = C col + b_row_off
   double alpha, beta;
   // LIST mode (list != nullptr): one entry per nb x nb tile, x = first row, y = first col | diag<<31;
-  // each tile is covered by sub*sub CTAs.
+  // each tile is covered by (tile/BM)*(tile/BN) CTAs (blockIdx.x = item * that + block inside the tile).
   const int2* list;
-  int sub;
-  int tile;  // nb: list tiles are clipped to tile x tile
+  int tile;  // nb: list tiles are clipped to tile x tile; a multiple of BM and BN
   // RECT mode: blocks (blockIdx.x, blockIdx.y) of the rectangle at (rect_row0, rect_col0);
   // lower != 0 keeps only elements on or below the rectangle's own diagonal.
   int rect_row0, rect_col0;
@@ -50,11 +63,13 @@ struct GemmParams {
 // (16 rows, cols, row-groups) so that a whole 128 x 16 slice arrives with ONE bulk copy; kind 2: plain
 // rank-2 view with 16 x 16 boxes; kind 4: panel in tile layout (rows = ntiles*ld, ld = tile size, cols = ld).
 // Returns 0 on success.
+// box_rows = rows of the operand one CTA loads per slice (BM for the A map, BN for the B map of the shape used).
 int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
-                     int kind);
+                     int kind, int box_rows = 128);
 
-// Launches the kernel for `nblocks_x` x `nblocks_y` CTAs on `stream`.
+// Launches the kernel for `nblocks_x` x `nblocks_y` CTAs on `stream`. The maps' boxes must match `shape`.
 cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
-                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y);
+                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y,
+                                GemmShape shape = GemmShape::k128x128);
 
 }  // namespace dlafb

@@ -24,14 +24,20 @@ bool dmma_ok<double>(int M, int N, const double* A, long long lda, const double*
 }
 
 cudaError_t gemm_nt_dmma_rect(cudaStream_t stream, int M, int N, int K, double alpha, const double* A, long long lda,
-                              const double* B, long long ldb, double beta, double* C, long long ldc, int lower) {
+                              const double* B, long long ldb, double beta, double* C, long long ldc, int lower,
+                              bool inplace) {
+  // few blocks = a launch whose duration is one CTA's serial chain of K/16 slices: use 4x more, smaller CTAs
+  // (the in-place product needs all N <= 128 columns in one CTA, so it splits the rows only)
+  const bool small = ceil_div(M, kBM) * ceil_div(N, kBN) < 120;
+  const GemmShape shape = !small ? GemmShape::k128x128 : inplace ? GemmShape::k32x128 : GemmShape::k64x64;
+  const int bm = shape_bm(shape), bn = shape_bn(shape);
   CUtensorMap ma, mb;
   int ka = (M % 16 == 0) ? 3 : 2, kb = (N % 16 == 0) ? 3 : 2;
-  if (ka == 3 && make_operand_map(&ma, A, M, K, lda, 3) != 0)
+  if (ka == 3 && make_operand_map(&ma, A, M, K, lda, 3, bm) != 0)
     ka = 2;
   if (ka == 2 && make_operand_map(&ma, A, M, K, lda, 2) != 0)
     return cudaErrorInvalidValue;
-  if (kb == 3 && make_operand_map(&mb, B, N, K, ldb, 3) != 0)
+  if (kb == 3 && make_operand_map(&mb, B, N, K, ldb, 3, bn) != 0)
     kb = 2;
   if (kb == 2 && make_operand_map(&mb, B, N, K, ldb, 2) != 0)
     return cudaErrorInvalidValue;
@@ -46,18 +52,19 @@ cudaError_t gemm_nt_dmma_rect(cudaStream_t stream, int M, int N, int K, double a
   p.lower = lower;
   p.nbox_a = ka == 3 ? 1 : 8;
   p.nbox_b = kb == 3 ? 1 : 8;
-  return launch_gemm_nt_dmma(stream, ma, mb, p, ceil_div(M, kBM), ceil_div(N, kBN));
+  return launch_gemm_nt_dmma(stream, ma, mb, p, ceil_div(M, bm), ceil_div(N, bn), shape);
 }
 
 template <class T>
 cudaError_t gemm_nt_dmma_try(cudaStream_t, int, int, int, typename Tr<T>::Real, const T*, long long, const T*,
-                             long long, typename Tr<T>::Real, T*, long long, int) {
+                             long long, typename Tr<T>::Real, T*, long long, int, bool) {
   return cudaErrorNotSupported;
 }
 template <>
 cudaError_t gemm_nt_dmma_try<double>(cudaStream_t s, int M, int N, int K, double alpha, const double* A, long long lda,
-                                     const double* B, long long ldb, double beta, double* C, long long ldc, int lower) {
-  return gemm_nt_dmma_rect(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower);
+                                     const double* B, long long ldb, double beta, double* C, long long ldc, int lower,
+                                     bool inplace) {
+  return gemm_nt_dmma_rect(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower, inplace);
 }
 
 }  // namespace
@@ -71,7 +78,7 @@ cudaError_t gemm_nt(cudaStream_t stream, int M, int N, int K, typename Tr<T>::Re
   if (dmma_ok<T>(M, N, A, lda, B, ldb, K)) {
     if (inplace && N > kBN)
       return cudaErrorInvalidValue;
-    return gemm_nt_dmma_try<T>(stream, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower);
+    return gemm_nt_dmma_try<T>(stream, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower, inplace);
   }
   if (inplace && N > kSimtTile)
     return cudaErrorInvalidValue;

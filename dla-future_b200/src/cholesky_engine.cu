@@ -43,6 +43,9 @@ struct dlafb_chol_plan {
 
 namespace {
 
+// launches with fewer 128 x 128 blocks than this use the 64 x 64 shape (148 SMs)
+constexpr size_t kSmallShapeBelow = 120;
+
 #define CU(x)                    \
   do {                           \
     cudaError_t e_ = (x);        \
@@ -103,7 +106,8 @@ struct Plan final : dlafb_chol_plan {
   size_t d_elems = 0;
   T* Pr[2] = {nullptr, nullptr};  // row panel: one nb x nb slot per local row tile
   T* Pc[2] = {nullptr, nullptr};  // transposed panel: one slot per local column tile
-  CUtensorMap map_pr[2], map_pc[2];
+  CUtensorMap map_pr[2], map_pc[2];      // boxes of 128 rows (throughput shape)
+  CUtensorMap map_pr_s[2], map_pc_s[2];  // boxes of 64 rows (latency shape, few tiles left)
   int2* lists = nullptr;
   std::vector<size_t> hp_off, np_off;
   int* info_dev = nullptr;
@@ -208,6 +212,10 @@ struct Plan final : dlafb_chol_plan {
             return -2;
           if (ct && make_operand_map(&map_pc[b], (const double*)Pc[b], (long long)ct * nb, nb, nb, 4) != 0)
             return -2;
+          if (rt && make_operand_map(&map_pr_s[b], (const double*)Pr[b], (long long)rt * nb, nb, nb, 4, 64) != 0)
+            return -2;
+          if (ct && make_operand_map(&map_pc_s[b], (const double*)Pc[b], (long long)ct * nb, nb, nb, 4, 64) != 0)
+            return -2;
         }
       }
     }
@@ -240,6 +248,9 @@ struct Plan final : dlafb_chol_plan {
   }
 
   // trailing update of the listed tiles: C(tile) -= rowpanel * colpanel^H
+  // The 64 x 64 shape takes over when the listed tiles no longer fill the chip with 128 x 128 blocks: each CTA is a
+  // serial chain of nb/16 slices, so 4x more, 4x shorter CTAs end the launch sooner (the look-ahead column and the
+  // last steps are on the critical path).
   int update(cudaStream_t s, T* A, int64_t ld, const CUtensorMap* map_a_local, int nbox_local, int64_t k, int buf,
              size_t off, size_t count) {
     if (count == 0)
@@ -254,15 +265,19 @@ struct Plan final : dlafb_chol_plan {
       p.alpha = -1.0;
       p.beta = 1.0;
       p.list = lists + off;
-      p.sub = (int)(nb / kBM);
       p.tile = (int)nb;
+      const size_t big = count * (nb / 128) * (nb / 128);
+      const bool small = big < kSmallShapeBelow;
+      const GemmShape shape = small ? GemmShape::k64x64 : GemmShape::k128x128;
+      const unsigned ctas = (unsigned)(small ? 4 * big : big);
       if (dist) {
         p.nbox_a = p.nbox_b = 4;
-        return (int)launch_gemm_nt_dmma(s, map_pr[buf], map_pc[buf], p, (unsigned)(count * p.sub * p.sub), 1);
+        return (int)launch_gemm_nt_dmma(s, small ? map_pr_s[buf] : map_pr[buf], small ? map_pc_s[buf] : map_pc[buf], p,
+                                        ctas, 1, shape);
       }
       p.a_col0 = p.b_col0 = (int)(k * nb);
       p.nbox_a = p.nbox_b = nbox_local;
-      return (int)launch_gemm_nt_dmma(s, *map_a_local, *map_a_local, p, (unsigned)(count * p.sub * p.sub), 1);
+      return (int)launch_gemm_nt_dmma(s, map_a_local[small ? 1 : 0], map_a_local[small ? 1 : 0], p, ctas, 1, shape);
     }
     SimtParams<T> p{};
     p.C = A;
@@ -290,15 +305,18 @@ struct Plan final : dlafb_chol_plan {
   }
 
   int factor_lower(T* A, int64_t ld) {
-    CUtensorMap map_local;
+    CUtensorMap map_local[2];  // [0] boxes of 128 rows, [1] of 64 rows
     int nbox_local = 1;
     if (fast && !dist && n > 0) {
       // rank-3 view reads whole 16-row groups: fine when the rows are a multiple of 16 or the columns are padded
       const int kind = (mloc % 16 == 0 || ld >= round_up(mloc, 16)) ? 3 : 2;
-      int r = make_operand_map(&map_local, (const double*)A, mloc, nloc, ld, kind);
+      int r = make_operand_map(&map_local[0], (const double*)A, mloc, nloc, ld, kind);
+      if (r == 0)
+        r = make_operand_map(&map_local[1], (const double*)A, mloc, nloc, ld, kind, 64);
       nbox_local = kind == 3 ? 1 : 8;
       if (r != 0 && kind == 3) {
-        r = make_operand_map(&map_local, (const double*)A, mloc, nloc, ld, 2);
+        r = make_operand_map(&map_local[0], (const double*)A, mloc, nloc, ld, 2);
+        map_local[1] = map_local[0];
         nbox_local = 8;
       }
       if (r != 0)
@@ -367,7 +385,7 @@ struct Plan final : dlafb_chol_plan {
         // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
         if (k >= 1)
           CU(cudaStreamWaitEvent(hp, ev_np[(k - 1) & 1], 0));
-        int r = update(hp, A, ld, &map_local, nbox_local, k, buf, hp_off[k], np_off[k] - hp_off[k]);
+        int r = update(hp, A, ld, map_local, nbox_local, k, buf, hp_off[k], np_off[k] - hp_off[k]);
         if (r != 0)
           return r;
         CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
@@ -375,7 +393,7 @@ struct Plan final : dlafb_chol_plan {
         const bool timed = profiling && np_cnt > 0;
         if (timed)
           CU(cudaEventRecord(pev[2 * k], np));
-        r = update(np, A, ld, &map_local, nbox_local, k, buf, np_off[k], np_cnt);
+        r = update(np, A, ld, map_local, nbox_local, k, buf, np_off[k], np_cnt);
         if (r != 0)
           return r;
         if (timed)
