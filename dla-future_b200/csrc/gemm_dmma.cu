@@ -55,6 +55,9 @@ __device__ __forceinline__ double lds_f64(uint32_t addr) {
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
@@ -121,7 +124,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   const int nk = p.K / kBK;
 
   // ---- pull this block of C into L2 while the contraction runs (the epilogue reads it) ----
-  if (p.beta != 0.0) {
+  if (p.beta != 0.0 && p.beta != 1.0) {
     const int rows = min(BM, m_lim - row0);
     const int cols = min(BN, n_lim - col0);
     const int segs = (rows + 15) >> 4;  // 128-byte lines per column
@@ -228,6 +231,34 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     // interior block: no predicates; the 16 loads of column group g+1 are in flight while group g is stored
     double* cb = p.C + (long long)(col0 + wn * (BN / 4) + 2 * kk) * p.ldc + (row0 + wm * (BM / 2) + r);
     const long long ldc = p.ldc;
+    double* c00 = p.C + (long long)col0 * ldc + row0;
+    if (beta == 1.0 && (reinterpret_cast<uintptr_t>(c00) & 15) == 0 && (ldc & 1) == 0) {
+      // C += alpha*acc without reading C into the SM: the block is staged in shared memory (the operand ring is
+      // free now) and added to global memory by bulk reduce copies, one per column; the adds execute in L2 and the
+      // CTA only waits until its shared memory has been read. One rounding per element, exactly like fma(1, c, v).
+      // Column stride BM*8 + 16 bytes: the 16 lanes of a half-warp (4 columns x 4 row pairs) hit 32 distinct banks.
+      constexpr uint32_t kColStride = BM * 8 + 16;
+      __syncthreads();  // every warp is done with the operand ring
+      const uint32_t mine = base + (wn * (BN / 4) + 2 * kk) * kColStride + (wm * (BM / 2) + r) * 8;
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int f = 0; f < F; ++f)
+            sts_f64(mine + (g * 8 + e) * kColStride + f * 64, alpha * acc[f][g][e]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();
+      if (threadIdx.x < BN) {
+        double* gp = c00 + (long long)threadIdx.x * ldc;
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;" ::"l"(gp),
+                     "r"(base + threadIdx.x * kColStride), "r"(BM * 8)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+      return;
+    }
     if (beta != 0.0) {
       double cv[2][2][F];
 #pragma unroll

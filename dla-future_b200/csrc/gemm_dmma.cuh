@@ -35,7 +35,10 @@ constexpr int shape_bn(GemmShape s) {
   return s == GemmShape::k64x64 ? 64 : 128;
 }
 constexpr int gemm_smem_bytes(int bm, int bn) {
-  return kStages * (bm + bn) * kBK * 8 + 2 * kStages * 8 + 1024;  // stages + barriers + align slack
+  // operand ring + barriers, or the staged block of C of the reduce epilogue (column stride bm*8 + 16), + align slack
+  const int ring = kStages * (bm + bn) * kBK * 8 + 2 * kStages * 8;
+  const int stage_c = bn * (bm * 8 + 16);
+  return (ring > stage_c ? ring : stage_c) + 1024;
 }
 
 struct GemmParams {
