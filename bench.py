@@ -159,6 +159,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
+    ap.add_argument("--timeline", default=None, help="write every rank's per-step timeline of the last step to PREFIX.rankR.json")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -227,6 +228,11 @@ def main():
         upd_ms, upd_fl, upd_n = upd_ms + m, upd_fl + f, upd_n + c
     launches = L.dlafb_launch_count() - l0 - args.steps  # minus the generator launch of every step
     clocks = sampler.stop() if rank == 0 else None
+    if args.timeline:
+        with open(f"{args.timeline}.rank{rank}.json", "w") as fh:
+            json.dump({"rank": rank, "grid": [P, Q], "n": n, "nb": nb,
+                       "ms": times[-1], "columns": ["start", "potrf", "panel", "row_bcast", "col_bcast", "lookahead",
+                                                     "bulk_begin", "bulk_end"], "steps": plan.timeline()}, fh)
     plan.set_profiling(False)
     info = plan.info()
     ms = sum(times) / len(times)

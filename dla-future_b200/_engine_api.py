@@ -41,6 +41,7 @@ ENGINE_API = {
     "dlafb_cholesky_plan_local_size": (c_int, [c_vp, P_i64, P_i64]),
     "dlafb_cholesky_plan_set_profiling": (c_int, [c_vp, c_int]),
     "dlafb_cholesky_plan_profile": (c_int, [c_vp, P_dbl, P_dbl, P_int]),
+    "dlafb_cholesky_plan_timeline": (c_int, [c_vp, P_dbl, ctypes.c_longlong]),
     "dlafb_launch_count": (ctypes.c_uint64, []),
 }
 
@@ -113,6 +114,7 @@ class CholeskyPlan:
         r, c = c_i64(), c_i64()
         _ck(L.dlafb_cholesky_plan_local_size(self.h, r, c), "local_size")
         self.local_rows, self.local_cols = r.value, c.value
+        self.nt = (n + nb - 1) // nb if n > 0 else 0
 
     def run(self, ptr, lda, stream):
         _ck(self.L.dlafb_cholesky_plan_run(self.h, ptr, lda, stream), "plan_run")
@@ -129,6 +131,12 @@ class CholeskyPlan:
         ms, fl, n = ctypes.c_double(), ctypes.c_double(), c_int()
         _ck(self.L.dlafb_cholesky_plan_profile(self.h, ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(n)), "profile")
         return ms.value, fl.value, n.value
+
+    def timeline(self):
+        """Rows of 8 times (ms since the start of the last profiled run), one row per step; see dlafb_engine.h."""
+        buf = (ctypes.c_double * (8 * max(self.nt, 1)))()
+        _ck(self.L.dlafb_cholesky_plan_timeline(self.h, buf, len(buf)), "timeline")
+        return [list(buf[8 * k:8 * k + 8]) for k in range(self.nt)]
 
     def close(self):
         if self.h:

@@ -3,7 +3,9 @@
 
 #include "common.cuh"
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 namespace dlafb {
 namespace {
@@ -67,52 +69,74 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // BM x BN block of C per CTA; 8 warps as 2 (rows) x 4 (cols), each owning (BM/2) x (BN/4) of it as F x G DMMA
 // fragments. 128 x 128 is the throughput shape; the smaller ones exist for the launches on the critical path of the
 // factorization (few CTAs, each a serial chain of K/16 slices at 128 flop/clk/SM).
+//
+// Persistent: CTA b works on blocks b, b + gridDim.x, ... The TMA producer (lane 0 of warp 0) keeps kPrefetch slices
+// in flight ACROSS block boundaries, so the first slices of the next block land while this block's epilogue runs;
+// measured fixed cost per block before: 5.2 us of 73.8 us at K = 512 (profiles/r01/update_kernel_alone.json).
+struct BlockCoord {
+  int trow, tcol;      // inside the tile (LIST) / rectangle (RECT)
+  int row0, col0;      // in C
+  int lower;           // keep only elements on or below the diagonal of the tile / rectangle
+  int m_lim, n_lim;    // clip
+  int b_from_a;        // LIST mode, diagonal tile: both operands come from the row panel (HERK)
+  int b_row_a;
+};
+
 template <int BM, int BN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-    gemm_nt_dmma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                        const GemmParams p) {
-  // ---- which block of C ----
-  constexpr int F = BM / 16, G = BN / 32;  // 8-row / 8-column fragments per warp
-  constexpr int kABytes = BM * kBK * 8, kBBytes = BN * kBK * 8, kStageB = kABytes + kBBytes;
-  static_assert(F >= 2 && G >= 2 && F % 2 == 0 && G % 2 == 0, "a warp owns whole 16-row groups of both operands");
-  int trow, tcol, row0, col0, lower, m_lim = p.m_total, n_lim = p.n_total;
-  int b_from_a = 0, b_row_a = 0;  // LIST mode, diagonal tile: both operands come from the row panel (HERK)
+__device__ __forceinline__ bool decode_block(const GemmParams& p, int id, BlockCoord& c) {
+  c.m_lim = p.m_total;
+  c.n_lim = p.n_total;
+  c.b_from_a = 0;
+  c.b_row_a = 0;
   if (p.list != nullptr) {
     const int sub_m = p.tile / BM, nsub = sub_m * (p.tile / BN);
-    const int item = blockIdx.x / nsub;
-    const int s = blockIdx.x - item * nsub;
+    const int item = id / nsub;
+    const int s = id - item * nsub;
     const int2 it = p.list[item];
-    lower = it.y < 0;
-    trow = (s % sub_m) * BM;
-    tcol = (s / sub_m) * BN;
-    row0 = it.x + trow;
-    col0 = (it.y & 0x7fffffff) + tcol;
-    b_from_a = lower;
-    b_row_a = it.x + tcol + p.a_row_off;
-    m_lim = min(m_lim, it.x + p.tile);
-    n_lim = min(n_lim, (it.y & 0x7fffffff) + p.tile);
+    c.lower = it.y < 0;
+    c.trow = (s % sub_m) * BM;
+    c.tcol = (s / sub_m) * BN;
+    c.row0 = it.x + c.trow;
+    c.col0 = (it.y & 0x7fffffff) + c.tcol;
+    c.b_from_a = c.lower;
+    c.b_row_a = it.x + c.tcol + p.a_row_off;
+    c.m_lim = min(c.m_lim, it.x + p.tile);
+    c.n_lim = min(c.n_lim, (it.y & 0x7fffffff) + p.tile);
   }
   else {
-    lower = p.lower;
-    trow = blockIdx.x * BM;
-    tcol = blockIdx.y * BN;
-    row0 = p.rect_row0 + trow;
-    col0 = p.rect_col0 + tcol;
+    const int by = id / p.rect_nx;
+    c.lower = p.lower;
+    c.trow = (id - by * p.rect_nx) * BM;
+    c.tcol = by * BN;
+    c.row0 = p.rect_row0 + c.trow;
+    c.col0 = p.rect_col0 + c.tcol;
   }
-  if (row0 >= m_lim || col0 >= n_lim)
-    return;
-  if (lower && trow + BM - 1 < tcol)
-    return;
+  if (c.row0 >= c.m_lim || c.col0 >= c.n_lim)
+    return false;
+  if (c.lower && c.trow + BM - 1 < c.tcol)
+    return false;
+  return true;
+}
+
+template <int BM, int BN, int STAGES, int MINB>
+__global__ void __launch_bounds__(kGemmThreads, MINB)
+    gemm_nt_dmma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                        const GemmParams p) {
+  constexpr int F = BM / 16, G = BN / 32;  // 8-row / 8-column fragments per warp
+  constexpr int kABytes = BM * kBK * 8, kBBytes = BN * kBK * 8, kStageB = kABytes + kBBytes;
+  constexpr uint32_t kColStride = BM * 8 + 16;  // staged C: the 16 lanes of a half-warp hit 32 distinct banks
+  static_assert(F >= 2 && G >= 2 && F % 2 == 0 && G % 2 == 0, "a warp owns whole 16-row groups of both operands");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_full = base + kStages * kStageB;
-  const uint32_t bar_empty = bar_full + 8 * kStages;
+  const uint32_t stg = base + STAGES * kStageB;  // half a block of C (BN/2 columns) for the reduce epilogue
+  const uint32_t bar_full = stg + (BN / 2) * kColStride;
+  const uint32_t bar_empty = bar_full + 8 * STAGES;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, 8);
     }
@@ -123,35 +147,34 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 
   const int nk = p.K / kBK;
 
-  // ---- pull this block of C into L2 while the contraction runs (the epilogue reads it) ----
-  if (p.beta != 0.0 && p.beta != 1.0) {
-    const int rows = min(BM, m_lim - row0);
-    const int cols = min(BN, n_lim - col0);
-    const int segs = (rows + 15) >> 4;  // 128-byte lines per column
-    for (int i = threadIdx.x; i < cols * segs; i += kGemmThreads) {
-      const int c = i / segs, sgm = i - c * segs;
-      const double* ptr = p.C + (long long)(col0 + c) * p.ldc + row0 + sgm * 16;
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
-    }
-  }
-
-  // ---- TMA producer role: lane 0 of warp 0 feeds the ring of stages, kPrefetch slices ahead of the math ----
+  // ---- TMA producer role: lane 0 of warp 0 feeds the ring of stages, (STAGES - 2) slices ahead of the math ----
   const bool producer = (threadIdx.x == 0);
-  const int a_row = row0 + p.a_row_off;
-  const int b_row = b_from_a ? b_row_a : col0 + p.b_row_off;
-  const CUtensorMap* mb = b_from_a ? &map_a : &map_b;
-  const int nbox_b = b_from_a ? p.nbox_a : p.nbox_b;
-  const int b_col0 = b_from_a ? p.a_col0 : p.b_col0;
-  auto issue = [&](int kt) {
-    const int s = kt % kStages;
-    const uint32_t ph = (kt / kStages) & 1;
+  int pr_id = blockIdx.x, pr_kt = 0;
+  uint32_t pr_g = 0;  // slices issued so far (stage = pr_g % STAGES)
+  BlockCoord pc;
+  bool pr_valid = false;
+  auto pr_seek = [&]() {
+    while (pr_id < p.ntiles && !decode_block<BM, BN>(p, pr_id, pc))
+      pr_id += gridDim.x;
+    pr_valid = pr_id < p.ntiles;
+    pr_kt = 0;
+  };
+  auto issue = [&]() {
+    if (!pr_valid)
+      return;
+    const int s = pr_g % STAGES;
+    const uint32_t ph = (pr_g / STAGES) & 1;
     mbar_wait(bar_empty + 8 * s, ph ^ 1);
     const uint32_t full = bar_full + 8 * s;
     mbar_expect_tx(full, kStageB);
     const uint32_t sa = base + s * kStageB;
     const uint32_t sb = sa + kABytes;
-    const int ka = p.a_col0 + kt * kBK;
-    const int kb = b_col0 + kt * kBK;
+    const int a_row = pc.row0 + p.a_row_off;
+    const int b_row = pc.b_from_a ? pc.b_row_a : pc.col0 + p.b_row_off;
+    const CUtensorMap* mb = pc.b_from_a ? &map_a : &map_b;
+    const int nbox_b = pc.b_from_a ? p.nbox_a : p.nbox_b;
+    const int ka = p.a_col0 + pr_kt * kBK;
+    const int kb = (pc.b_from_a ? p.a_col0 : p.b_col0) + pr_kt * kBK;
     if (p.nbox_a == 1)
       tma_load_3d(sa, &map_a, 0, ka, a_row >> 4, full);
     else if (p.nbox_a == 4)
@@ -159,30 +182,34 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
     else
       for (int g = 0; g < BM / 16; ++g)
         tma_load_2d(sa + g * kGroupBytes, &map_a, a_row + 16 * g, ka, full);
+    // a diagonal tile takes B through the A map, whose box has BM rows: BN / BM copies
+    const int bbox = pc.b_from_a ? BM : BN;
     if (nbox_b == 1)
-      tma_load_3d(sb, mb, 0, kb, b_row >> 4, full);
+      for (int i = 0; i < BN; i += bbox)
+        tma_load_3d(sb + i * 128, mb, 0, kb, (b_row + i) >> 4, full);
     else if (nbox_b == 4)
-      tma_load_4d(sb, mb, 0, kb, (b_row % p.tile) >> 4, b_row / p.tile, full);
+      for (int i = 0; i < BN; i += bbox)
+        tma_load_4d(sb + i * 128, mb, 0, kb, ((b_row + i) % p.tile) >> 4, (b_row + i) / p.tile, full);
     else
       for (int g = 0; g < BN / 16; ++g)
         tma_load_2d(sb + g * kGroupBytes, mb, b_row + 16 * g, kb, full);
+    ++pr_g;
+    if (++pr_kt == nk) {
+      pr_id += gridDim.x;
+      pr_seek();
+    }
   };
-  if (producer)
-    for (int kt = 0; kt < kPrefetch && kt < nk; ++kt)
-      issue(kt);
+  if (producer) {
+    pr_seek();
+    for (int i = 0; i < (STAGES - 2); ++i)
+      issue();
+  }
 
   // ---- DMMA: 8 warps as 2 (rows) x 4 (cols); each owns a (BM/2) x (BN/4) block of C ----
   const int wm = warp & 1;
   const int wn = warp >> 1;
   const int r = lane >> 2;   // fragment row (A) / column (B)
   const int kk = lane & 3;   // fragment k index; MMA step s4 uses k-columns 8*(s4/2) + 2*kk + (s4&1)
-
-  double acc[F][G][2];
-#pragma unroll
-  for (int f = 0; f < F; ++f)
-#pragma unroll
-    for (int g = 0; g < G; ++g)
-      acc[f][g][0] = acc[f][g][1] = 0.0;
 
   // Swizzle<3,4,3> of the 128B rows: 16-byte chunk index ^= (k-column & 7). With the k permutation above
   // the 16 lanes of a half-warp hit 16 distinct 8-byte bank pairs.
@@ -195,128 +222,165 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   const uint32_t a_thr = (wm * (F / 2)) * kGroupBytes + (2 * kk) * 128;
   const uint32_t b_thr = kABytes + (wn * (G / 2)) * kGroupBytes + (2 * kk) * 128;
 
-  for (int kt = 0; kt < nk; ++kt) {
-    // refill the stage freed two slices ago: its empty barrier is (almost always) already complete
-    if (producer && kt + kPrefetch < nk)
-      issue(kt + kPrefetch);
-    const int s = kt % kStages;
-    const uint32_t ph = (kt / kStages) & 1;
-    mbar_wait(bar_full + 8 * s, ph);
-    const uint32_t st = base + s * kStageB;
+  uint32_t cg = 0;          // slices consumed so far
+  bool stg_pending = false;  // bulk copies of the previous block may still be reading the staging buffer
+
+  for (int id = blockIdx.x; id < p.ntiles; id += gridDim.x) {
+    BlockCoord c;
+    if (!decode_block<BM, BN>(p, id, c))
+      continue;
+    const int row0 = c.row0, col0 = c.col0, m_lim = c.m_lim, n_lim = c.n_lim;
+
+    // pull this block of C into L2 while the contraction runs (only when the epilogue reads it)
+    if (p.beta != 0.0 && p.beta != 1.0) {
+      const int rows = min(BM, m_lim - row0);
+      const int cols = min(BN, n_lim - col0);
+      const int segs = (rows + 15) >> 4;  // 128-byte lines per column
+      for (int i = threadIdx.x; i < cols * segs; i += kGemmThreads) {
+        const int cc = i / segs, sgm = i - cc * segs;
+        const double* ptr = p.C + (long long)(col0 + cc) * p.ldc + row0 + sgm * 16;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+      }
+    }
+
+    double acc[F][G][2];
 #pragma unroll
-    for (int s4 = 0; s4 < 4; ++s4) {
-      const uint32_t koff = (8 * (s4 >> 1) + (s4 & 1)) * 128;
-      double a[F], b[G];
-#pragma unroll
-      for (int f = 0; f < F; ++f)
-        a[f] = lds_f64(st + a_thr + (f >> 1) * kGroupBytes + koff + xo[f & 1][s4 & 1]);
+    for (int f = 0; f < F; ++f)
 #pragma unroll
       for (int g = 0; g < G; ++g)
-        b[g] = lds_f64(st + b_thr + (g >> 1) * kGroupBytes + koff + xo[g & 1][s4 & 1]);
+        acc[f][g][0] = acc[f][g][1] = 0.0;
+
+    for (int kt = 0; kt < nk; ++kt, ++cg) {
+      // refill the stage freed two slices ago: its empty barrier is (almost always) already complete
+      if (producer)
+        issue();
+      const int s = cg % STAGES;
+      const uint32_t ph = (cg / STAGES) & 1;
+      mbar_wait(bar_full + 8 * s, ph);
+      const uint32_t st = base + s * kStageB;
 #pragma unroll
-      for (int f = 0; f < F; ++f)
+      for (int s4 = 0; s4 < 4; ++s4) {
+        const uint32_t koff = (8 * (s4 >> 1) + (s4 & 1)) * 128;
+        double a[F], b[G];
+#pragma unroll
+        for (int f = 0; f < F; ++f)
+          a[f] = lds_f64(st + a_thr + (f >> 1) * kGroupBytes + koff + xo[f & 1][s4 & 1]);
 #pragma unroll
         for (int g = 0; g < G; ++g)
-          dmma884(acc[f][g][0], acc[f][g][1], a[f], b[g]);
-    }
-    __syncwarp();
-    if (lane == 0)
-      mbar_arrive(bar_empty + 8 * s);
-  }
-
-  // ---- epilogue: C <- beta*C + alpha*acc, clipped and (optionally) restricted to the lower triangle ----
-  const double alpha = p.alpha, beta = p.beta;
-  const bool full_block = !lower || (trow >= tcol + BN - 1);
-  if (full_block && row0 + BM <= m_lim && col0 + BN <= n_lim) {
-    // interior block: no predicates; the 16 loads of column group g+1 are in flight while group g is stored
-    double* cb = p.C + (long long)(col0 + wn * (BN / 4) + 2 * kk) * p.ldc + (row0 + wm * (BM / 2) + r);
-    const long long ldc = p.ldc;
-    double* c00 = p.C + (long long)col0 * ldc + row0;
-    if (beta == 1.0 && (reinterpret_cast<uintptr_t>(c00) & 15) == 0 && (ldc & 1) == 0) {
-      // C += alpha*acc without reading C into the SM: the block is staged in shared memory (the operand ring is
-      // free now) and added to global memory by bulk reduce copies, one per column; the adds execute in L2 and the
-      // CTA only waits until its shared memory has been read. One rounding per element, exactly like fma(1, c, v).
-      // Column stride BM*8 + 16 bytes: the 16 lanes of a half-warp (4 columns x 4 row pairs) hit 32 distinct banks.
-      constexpr uint32_t kColStride = BM * 8 + 16;
-      __syncthreads();  // every warp is done with the operand ring
-      const uint32_t mine = base + (wn * (BN / 4) + 2 * kk) * kColStride + (wm * (BM / 2) + r) * 8;
+          b[g] = lds_f64(st + b_thr + (g >> 1) * kGroupBytes + koff + xo[g & 1][s4 & 1]);
 #pragma unroll
-      for (int g = 0; g < G; ++g)
+        for (int f = 0; f < F; ++f)
+#pragma unroll
+          for (int g = 0; g < G; ++g)
+            dmma884(acc[f][g][0], acc[f][g][1], a[f], b[g]);
+      }
+      __syncwarp();
+      if (lane == 0)
+        mbar_arrive(bar_empty + 8 * s);
+    }
+
+    // ---- epilogue: C <- beta*C + alpha*acc, clipped and (optionally) restricted to the lower triangle ----
+    const double alpha = p.alpha, beta = p.beta;
+    const bool full_block = !c.lower || (c.trow >= c.tcol + BN - 1);
+    const long long ldc = p.ldc;
+    if (full_block && row0 + BM <= m_lim && col0 + BN <= n_lim) {
+      double* c00 = p.C + (long long)col0 * ldc + row0;
+      if (beta == 1.0 && (reinterpret_cast<uintptr_t>(c00) & 15) == 0 && (ldc & 1) == 0) {
+        // C += alpha*acc without reading C into the SM: half a block at a time is staged in shared memory and added
+        // to global memory by bulk reduce copies, one per column; the adds execute in L2 while this CTA goes on
+        // with the next block. One rounding per element, exactly like fma(1, c, v).
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (stg_pending && threadIdx.x < BN / 2)
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          __syncthreads();  // staging buffer free
+          if ((wn >> 1) == h) {
+            const uint32_t mine = stg + ((wn & 1) * (BN / 4) + 2 * kk) * kColStride + (wm * (BM / 2) + r) * 8;
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+#pragma unroll
+              for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int f = 0; f < F; ++f)
+                  sts_f64(mine + (g * 8 + e) * kColStride + f * 64, alpha * acc[f][g][e]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          }
+          __syncthreads();
+          if (threadIdx.x < BN / 2) {
+            double* gp = c00 + (long long)(h * (BN / 2) + threadIdx.x) * ldc;
+            asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;" ::"l"(gp),
+                         "r"(stg + threadIdx.x * kColStride), "r"(BM * 8)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          stg_pending = true;
+        }
+        continue;
+      }
+      // interior block: no predicates; the loads of column group g+1 are in flight while group g is stored
+      double* cb = p.C + (long long)(col0 + wn * (BN / 4) + 2 * kk) * ldc + (row0 + wm * (BM / 2) + r);
+      if (beta != 0.0) {
+        double cv[2][2][F];
 #pragma unroll
         for (int e = 0; e < 2; ++e)
 #pragma unroll
           for (int f = 0; f < F; ++f)
-            sts_f64(mine + (g * 8 + e) * kColStride + f * 64, alpha * acc[f][g][e]);
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      __syncthreads();
-      if (threadIdx.x < BN) {
-        double* gp = c00 + (long long)threadIdx.x * ldc;
-        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;" ::"l"(gp),
-                     "r"(base + threadIdx.x * kColStride), "r"(BM * 8)
-                     : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      }
-      return;
-    }
-    if (beta != 0.0) {
-      double cv[2][2][F];
+            cv[0][e][f] = __ldcg(cb + e * ldc + f * 8);
 #pragma unroll
-      for (int e = 0; e < 2; ++e)
+        for (int g = 0; g < G; ++g) {
+          if (g + 1 < G) {
 #pragma unroll
-        for (int f = 0; f < F; ++f)
-          cv[0][e][f] = __ldcg(cb + e * ldc + f * 8);
+            for (int e = 0; e < 2; ++e)
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        if (g + 1 < G) {
+              for (int f = 0; f < F; ++f)
+                cv[(g + 1) & 1][e][f] = __ldcg(cb + ((g + 1) * 8 + e) * ldc + f * 8);
+          }
 #pragma unroll
           for (int e = 0; e < 2; ++e)
 #pragma unroll
             for (int f = 0; f < F; ++f)
-              cv[(g + 1) & 1][e][f] = __ldcg(cb + ((g + 1) * 8 + e) * ldc + f * 8);
+              __stcg(cb + (g * 8 + e) * ldc + f * 8, fma(beta, cv[g & 1][e][f], alpha * acc[f][g][e]));
         }
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-          for (int f = 0; f < F; ++f)
-            __stcg(cb + (g * 8 + e) * ldc + f * 8, fma(beta, cv[g & 1][e][f], alpha * acc[f][g][e]));
       }
+      else {
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+          for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int f = 0; f < F; ++f)
+              __stcg(cb + (g * 8 + e) * ldc + f * 8, alpha * acc[f][g][e]);
+      }
+      continue;
     }
-    else {
 #pragma unroll
-      for (int g = 0; g < G; ++g)
+    for (int g = 0; g < G; ++g) {
 #pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-          for (int f = 0; f < F; ++f)
-            __stcg(cb + (g * 8 + e) * ldc + f * 8, alpha * acc[f][g][e]);
-    }
-    return;
-  }
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int cl = wn * (BN / 4) + g * 8 + 2 * kk + e;  // column inside the CTA block
-      const int c = col0 + cl;
-      if (c >= n_lim)
-        continue;
-      double* colp = p.C + (long long)c * p.ldc;
-#pragma unroll
-      for (int f = 0; f < F; ++f) {
-        const int rl = wm * (BM / 2) + f * 8 + r;
-        const int rr = row0 + rl;
-        if (rr >= m_lim)
+      for (int e = 0; e < 2; ++e) {
+        const int cl = wn * (BN / 4) + g * 8 + 2 * kk + e;  // column inside the CTA block
+        const int cc = col0 + cl;
+        if (cc >= n_lim)
           continue;
-        if (!full_block && (trow + rl < tcol + cl))
-          continue;
-        double v = alpha * acc[f][g][e];
-        if (beta != 0.0)
-          v = fma(beta, colp[rr], v);
-        colp[rr] = v;
+        double* colp = p.C + (long long)cc * ldc;
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+          const int rl = wm * (BM / 2) + f * 8 + r;
+          const int rr = row0 + rl;
+          if (rr >= m_lim)
+            continue;
+          if (!full_block && (c.trow + rl < c.tcol + cl))
+            continue;
+          double v = alpha * acc[f][g][e];
+          if (beta != 0.0)
+            v = fma(beta, colp[rr], v);
+          colp[rr] = v;
+        }
       }
     }
   }
+  // the staging buffer must outlive the bulk copies that read it
+  if (stg_pending && threadIdx.x < BN / 2)
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -379,15 +443,39 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
 }
 
 namespace {
-template <int BM, int BN>
-cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b, const GemmParams& p,
+int sm_count() {
+  static int n = [] {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    return v;
+  }();
+  return n;
+}
+
+template <int BM, int BN, int STAGES, int MINB>
+cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b, GemmParams p,
                          unsigned nx, unsigned ny) {
-  constexpr int smem = gemm_smem_bytes(BM, BN);
-  static cudaError_t attr =
-      cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  constexpr int smem = gemm_smem_bytes(BM, BN, STAGES);
+  static_assert(MINB * (smem + 1024) <= 228 * 1024, "MINB CTAs must fit the SM's shared memory");
+  static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN, STAGES, MINB>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (attr != cudaSuccess)
     return attr;
-  gemm_nt_dmma_kernel<BM, BN><<<dim3(nx, ny), kGemmThreads, smem, stream>>>(map_a, map_b, p);
+  p.ntiles = (int)(nx * ny);
+  p.rect_nx = (int)nx;
+  // One block per CTA by default: a persistent grid would keep every SM busy for the whole launch and starve the
+  // high-priority stream (diagonal tile, panel solve, look-ahead column), which gets an SM only when a CTA retires.
+  // DLAFB_GEMM_PERSISTENT=1 makes CTA b loop over blocks b, b + grid, ... (kernel microbenchmarks).
+  static const bool persistent = [] {
+    const char* e = getenv("DLAFB_GEMM_PERSISTENT");
+    return e && e[0] == '1';
+  }();
+  unsigned grid = (unsigned)p.ntiles;
+  if (persistent)
+    grid = std::min<unsigned>(grid, (unsigned)sm_count() * MINB);
+  gemm_nt_dmma_kernel<BM, BN, STAGES, MINB><<<grid, kGemmThreads, smem, stream>>>(map_a, map_b, p);
   ++g_launches;
   return cudaGetLastError();
 }
@@ -399,11 +487,13 @@ cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, c
     return cudaSuccess;
   switch (shape) {
     case GemmShape::k128x128:
-      return launch_shape<128, 128>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      return launch_shape<128, 128, 4, 1>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
     case GemmShape::k64x64:
-      return launch_shape<64, 64>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      return launch_shape<64, 64, 4, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
     case GemmShape::k32x128:
-      return launch_shape<32, 128>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      return launch_shape<32, 128, 4, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+    case GemmShape::k64x128:
+      return launch_shape<64, 128, 3, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
   }
   return cudaErrorInvalidValue;
 }

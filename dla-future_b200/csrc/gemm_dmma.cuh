@@ -27,18 +27,17 @@ constexpr int kPrefetch = kStages - 2;  // slices in flight ahead of the math (r
 // Block of C per CTA. 128 x 128 is the throughput shape (88 % of the DMMA peak); one CTA needs 2.1 us per K-slice of
 // 16 whatever the shape's area ratio, so the launches on the critical path (few blocks, K = 128..512) use the small
 // shapes: 4x (64 x 64) or 4x (32 x 128, the in-place panel solve needs all N columns in one CTA) more CTAs.
-enum class GemmShape : int { k128x128 = 0, k64x64 = 1, k32x128 = 2 };
+enum class GemmShape : int { k128x128 = 0, k64x64 = 1, k32x128 = 2, k64x128 = 3 };
+constexpr GemmShape kDefaultBulkShape = GemmShape::k64x128;  // two co-resident CTAs hide each other's prologue and epilogue
 constexpr int shape_bm(GemmShape s) {
-  return s == GemmShape::k128x128 ? 128 : s == GemmShape::k64x64 ? 64 : 32;
+  return s == GemmShape::k128x128 ? 128 : (s == GemmShape::k64x64 || s == GemmShape::k64x128) ? 64 : 32;
 }
 constexpr int shape_bn(GemmShape s) {
   return s == GemmShape::k64x64 ? 64 : 128;
 }
-constexpr int gemm_smem_bytes(int bm, int bn) {
-  // operand ring + barriers, or the staged block of C of the reduce epilogue (column stride bm*8 + 16), + align slack
-  const int ring = kStages * (bm + bn) * kBK * 8 + 2 * kStages * 8;
-  const int stage_c = bn * (bm * 8 + 16);
-  return (ring > stage_c ? ring : stage_c) + 1024;
+constexpr int gemm_smem_bytes(int bm, int bn, int stages = kStages) {
+  // operand ring + half a staged block of C for the reduce epilogue (column stride bm*8 + 16) + barriers + align slack
+  return stages * (bm + bn) * kBK * 8 + (bn / 2) * (bm * 8 + 16) + 2 * stages * 8 + 1024;
 }
 
 struct GemmParams {
@@ -57,6 +56,7 @@ struct GemmParams {
   // lower != 0 keeps only elements on or below the rectangle's own diagonal.
   int rect_row0, rect_col0;
   int lower;
+  int ntiles, rect_nx;  // filled by the launcher: number of blocks, blocks per rectangle row
   // 1: rank-3 map (one TMA per operand slice), 8: rank-2 map (one TMA per 16-row group),
   // 4: rank-4 map of a panel stored as contiguous tile x tile tiles (one TMA per slice)
   int nbox_a, nbox_b;

@@ -1,6 +1,7 @@
 // Host-side composition of the tile kernels (see tile_ops.cuh). Nothing here synchronises or allocates.
 #include "tile_ops.cuh"
 
+#include <cstdlib>
 #include <type_traits>
 
 #include "gemm_dmma.cuh"
@@ -29,7 +30,11 @@ cudaError_t gemm_nt_dmma_rect(cudaStream_t stream, int M, int N, int K, double a
   // few blocks = a launch whose duration is one CTA's serial chain of K/16 slices: use 4x more, smaller CTAs
   // (the in-place product needs all N <= 128 columns in one CTA, so it splits the rows only)
   const bool small = ceil_div(M, kBM) * ceil_div(N, kBN) < 120;
-  const GemmShape shape = !small ? GemmShape::k128x128 : inplace ? GemmShape::k32x128 : GemmShape::k64x64;
+  static const GemmShape big_shape = [] {
+    const char* e = getenv("DLAFB_BULK_SHAPE");
+    return (e && e[0] == '0') ? GemmShape::k128x128 : (e && e[0] == '3') ? GemmShape::k64x128 : kDefaultBulkShape;
+  }();
+  const GemmShape shape = !small ? big_shape : inplace ? GemmShape::k32x128 : GemmShape::k64x64;
   const int bm = shape_bm(shape), bn = shape_bn(shape);
   CUtensorMap ma, mb;
   int ka = (M % 16 == 0) ? 3 : 2, kb = (N % 16 == 0) ? 3 : 2;

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <type_traits>
+#include <cstdlib>
 #include <vector>
 
 #include "../../include/dlafb_engine.h"
@@ -38,6 +39,7 @@ struct dlafb_chol_plan {
   virtual int info(int* out) = 0;
   virtual void local_size(int64_t* r, int64_t* c) = 0;
   virtual int profile(double* ms, double* flops, int* launches) = 0;
+  virtual int timeline(double* out, long long cap) = 0;
   bool profiling = false;
 };
 
@@ -45,6 +47,15 @@ namespace {
 
 // launches with fewer 128 x 128 blocks than this use the 64 x 64 shape (148 SMs)
 constexpr size_t kSmallShapeBelow = 120;
+
+// shape of the bulk launches (DLAFB_BULK_SHAPE=0: one 128 x 128 CTA per SM, 3: two 64 x 128 CTAs per SM)
+GemmShape bulk_shape() {
+  static const GemmShape s = [] {
+    const char* e = getenv("DLAFB_BULK_SHAPE");
+    return (e && e[0] == '0') ? GemmShape::k128x128 : (e && e[0] == '3') ? GemmShape::k64x128 : kDefaultBulkShape;
+  }();
+  return s;
+}
 
 #define CU(x)                    \
   do {                           \
@@ -115,6 +126,10 @@ struct Plan final : dlafb_chol_plan {
   int64_t ldt = 0;
   // profiling of the bulk (np stream) update launches: one timed event pair per step
   std::vector<cudaEvent_t> pev;
+  // ... and of the high-priority stream: per step [start, diagonal tile done, panel solved + packed, row broadcast
+  // done, column broadcasts done, look-ahead column updated], plus the start of the run
+  std::vector<cudaEvent_t> hev;
+  cudaEvent_t ev_t0 = nullptr;
   std::vector<double> np_flops;
   std::vector<char> np_timed;
 
@@ -134,6 +149,35 @@ struct Plan final : dlafb_chol_plan {
     cudaFree(tbuf);
     for (cudaEvent_t e : pev)
       cudaEventDestroy(e);
+    for (cudaEvent_t e : hev)
+      cudaEventDestroy(e);
+    if (ev_t0) cudaEventDestroy(ev_t0);
+  }
+
+  // per step 8 times in ms since the start of the last profiled run: the 6 hp marks, then begin/end of the bulk update
+  // (-1 where a mark was not recorded)
+  int timeline(double* out, long long cap) override {
+    CU(cudaStreamSynchronize(hp));
+    CU(cudaStreamSynchronize(np));
+    if (hev.empty() || cap < nt * 8)
+      return 1;
+    for (int64_t k = 0; k < nt; ++k) {
+      for (int i = 0; i < 8; ++i)
+        out[k * 8 + i] = -1.0;
+      if (k == nt - 1)
+        continue;
+      float x = 0;
+      for (int i = 0; i < 6; ++i) {
+        CU(cudaEventElapsedTime(&x, ev_t0, hev[6 * k + i]));
+        out[k * 8 + i] = x;
+      }
+      if (np_timed[k])
+        for (int i = 0; i < 2; ++i) {
+          CU(cudaEventElapsedTime(&x, ev_t0, pev[2 * k + i]));
+          out[k * 8 + 6 + i] = x;
+        }
+    }
+    return 0;
   }
 
   // algorithmic flops of one update tile (real flops; complex multiply-add = 8)
@@ -267,17 +311,17 @@ struct Plan final : dlafb_chol_plan {
       p.list = lists + off;
       p.tile = (int)nb;
       const size_t big = count * (nb / 128) * (nb / 128);
-      const bool small = big < kSmallShapeBelow;
-      const GemmShape shape = small ? GemmShape::k64x64 : GemmShape::k128x128;
-      const unsigned ctas = (unsigned)(small ? 4 * big : big);
+      const GemmShape shape = big < kSmallShapeBelow ? GemmShape::k64x64 : bulk_shape();
+      const int bm = shape_bm(shape), bn = shape_bn(shape);
+      const unsigned ctas = (unsigned)(count * (nb / bm) * (nb / bn));
       if (dist) {
         p.nbox_a = p.nbox_b = 4;
-        return (int)launch_gemm_nt_dmma(s, small ? map_pr_s[buf] : map_pr[buf], small ? map_pc_s[buf] : map_pc[buf], p,
-                                        ctas, 1, shape);
+        return (int)launch_gemm_nt_dmma(s, bm == 64 ? map_pr_s[buf] : map_pr[buf], bn == 64 ? map_pc_s[buf] : map_pc[buf],
+                                        p, ctas, 1, shape);
       }
       p.a_col0 = p.b_col0 = (int)(k * nb);
       p.nbox_a = p.nbox_b = nbox_local;
-      return (int)launch_gemm_nt_dmma(s, map_a_local[small ? 1 : 0], map_a_local[small ? 1 : 0], p, ctas, 1, shape);
+      return (int)launch_gemm_nt_dmma(s, map_a_local[bm == 64 ? 1 : 0], map_a_local[bn == 64 ? 1 : 0], p, ctas, 1, shape);
     }
     SimtParams<T> p{};
     p.C = A;
@@ -334,10 +378,15 @@ struct Plan final : dlafb_chol_plan {
       const int nk = (int)sched.rows.tile_size(k);
       const bool last = (k == nt - 1);
       T* Akk = nullptr;
+      const bool mark = profiling && !last;
+      if (mark)
+        CU(cudaEventRecord(hev[6 * k + 0], hp));
       if (st.own_diag) {
         Akk = A + (size_t)st.lk_row * nb + (size_t)st.lk_col * nb * ld;
         CU(potrf_tile<T>(hp, 'L', nk, Akk, ld, DW, ib, info_dev, (int)(k * nb)));
       }
+      if (mark)
+        CU(cudaEventRecord(hev[6 * k + 1], hp));
       if (!last) {
         if (!dist) {
           const int m_below = (int)(n - (k + 1) * nb);
@@ -359,11 +408,15 @@ struct Plan final : dlafb_chol_plan {
               CU(pack_tiles<T>(hp, m_below, (int)nb, B, ld, Pr[buf] + (size_t)st.il0 * slot, (int)nb));
             }
           }
+          if (mark)
+            CU(cudaEventRecord(hev[6 * k + 2], hp));
           const size_t row_cnt = (size_t)(st.il_end - st.il0) * slot;
           if (Q > 1 && row_cnt > 0) {
             T* p = Pr[buf] + (size_t)st.il0 * slot;
             NC(ncclBroadcast(p, p, row_cnt * mult, nt_, st.row_root, rowc, hp));
           }
+          if (mark)
+            CU(cudaEventRecord(hev[6 * k + 3], hp));
           if (!st.colb.empty()) {
             if (P > 1) {
               NC(ncclGroupStart());
@@ -381,6 +434,13 @@ struct Plan final : dlafb_chol_plan {
             }
           }
         }
+        if (mark) {
+          if (!dist) {
+            CU(cudaEventRecord(hev[6 * k + 2], hp));
+            CU(cudaEventRecord(hev[6 * k + 3], hp));
+          }
+          CU(cudaEventRecord(hev[6 * k + 4], hp));
+        }
         CU(cudaEventRecord(ev_panel[buf], hp));
         // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
         if (k >= 1)
@@ -388,6 +448,8 @@ struct Plan final : dlafb_chol_plan {
         int r = update(hp, A, ld, map_local, nbox_local, k, buf, hp_off[k], np_off[k] - hp_off[k]);
         if (r != 0)
           return r;
+        if (mark)
+          CU(cudaEventRecord(hev[6 * k + 5], hp));
         CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
         const size_t np_cnt = (k + 1 < nt ? hp_off[k + 1] : np_off[k]) - np_off[k];
         const bool timed = profiling && np_cnt > 0;
@@ -412,7 +474,15 @@ struct Plan final : dlafb_chol_plan {
       for (cudaEvent_t& e : pev)
         CU(cudaEventCreate(&e));
     }
+    if (profiling && hev.empty()) {
+      hev.resize(6 * nt);
+      for (cudaEvent_t& e : hev)
+        CU(cudaEventCreate(&e));
+      CU(cudaEventCreate(&ev_t0));
+    }
     np_timed.assign(nt + 1, 0);
+    if (profiling)
+      CU(cudaEventRecord(ev_t0, user));
     CU(cudaEventRecord(ev_in, user));
     CU(cudaStreamWaitEvent(hp, ev_in, 0));
     CU(cudaStreamWaitEvent(np, ev_in, 0));
@@ -514,6 +584,12 @@ int dlafb_cholesky_plan_set_profiling(dlafb_chol_plan_t plan, int on) {
     return -1;
   plan->profiling = on != 0;
   return 0;
+}
+
+int dlafb_cholesky_plan_timeline(dlafb_chol_plan_t plan, double* out, long long cap) {
+  if (!plan || !out)
+    return 1;
+  return plan->timeline(out, cap);
 }
 
 int dlafb_cholesky_plan_profile(dlafb_chol_plan_t plan, double* update_ms, double* update_flops, int* launches) {

@@ -7,6 +7,7 @@
 //   loop structure           include/dlaf/factorization/cholesky/impl.h:191-313
 //   panel broadcast routing  include/dlaf/communication/broadcast_panel.h:123-213
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <vector>
 
@@ -59,7 +60,7 @@ struct Step {
   int il0 = 0, jl0 = 0;    // first local row / column tile with global index > k
   int il_end = 0, jl_end = 0;
   std::vector<ColBcast> colb;
-  std::vector<UpdateTile> hp, np;  // trailing tiles of global column k+1 (look-ahead) and the rest, column-major
+  std::vector<UpdateTile> hp, np;  // trailing tiles of global column k+1 (look-ahead) and the rest, in row bands
 };
 
 struct Schedule {
@@ -98,12 +99,20 @@ inline Schedule make_schedule(int64_t n, int64_t nb, int P, int Q, int pr, int p
         continue;  // the last tile has nothing below it: not needed in the transposed panel (:186-191)
       st.colb.push_back(ColBcast{jl, g, R.owner(g), (int)R.local_of(g)});
     }
-    for (int jl = st.jl0; jl < st.jl_end; ++jl) {
-      const int64_t gj = C.global_of(jl);
-      for (int il = (int)R.next_local(gj); il < st.il_end; ++il) {
-        const int64_t gi = R.global_of(il);
-        UpdateTile t{(int)(il * nb), (int)(jl * nb), gi == gj ? 1 : 0};
-        (gj == k + 1 ? st.hp : st.np).push_back(t);
+    // Bands of kBandTiles local tile rows, column after column inside a band: the band's tiles of the row panel stay
+    // in L2 while the column-panel tiles stream through once per band. (Plain column-major order re-read the whole
+    // row panel from HBM for every tile column: 7.9 GB read instead of 4.2 GB for the first update of n = 32768,
+    // profiles/r01/ncu_update_kernel.txt.)
+    const int kBandTiles = (int)std::max<int64_t>(1, 4096 / nb);  // 16 MB of FP64 row panel at nb = 512
+    for (int ib0 = st.il0; ib0 < st.il_end; ib0 += kBandTiles) {
+      const int ib1 = std::min(ib0 + kBandTiles, st.il_end);
+      for (int jl = st.jl0; jl < st.jl_end; ++jl) {
+        const int64_t gj = C.global_of(jl);
+        for (int il = std::max((int)R.next_local(gj), ib0); il < ib1; ++il) {
+          const int64_t gi = R.global_of(il);
+          UpdateTile t{(int)(il * nb), (int)(jl * nb), gi == gj ? 1 : 0};
+          (gj == k + 1 ? st.hp : st.np).push_back(t);
+        }
       }
     }
   }

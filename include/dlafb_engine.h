@@ -83,6 +83,10 @@ int dlafb_cholesky_plan_local_size(dlafb_chol_plan_t plan, int64_t* rows, int64_
  * dlafb_cholesky_plan_profile returns their summed duration, their algorithmic flops and their number. */
 int dlafb_cholesky_plan_set_profiling(dlafb_chol_plan_t plan, int on);
 int dlafb_cholesky_plan_profile(dlafb_chol_plan_t plan, double* update_ms, double* update_flops, int* launches);
+/* Timeline of the last profiled run: 8 times per step (ms since the run started on the caller's stream): step start,
+ * diagonal tile factored, panel solved and packed, row broadcast done, column broadcasts done, look-ahead column
+ * updated (all on the high-priority stream), bulk update begin / end. -1 where not recorded. out holds >= 8*nt. */
+int dlafb_cholesky_plan_timeline(dlafb_chol_plan_t plan, double* out, long long cap);
 
 /* Kernels launched by this library so far in this process. */
 uint64_t dlafb_launch_count(void);
