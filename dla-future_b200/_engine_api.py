@@ -39,6 +39,7 @@ ENGINE_API = {
     "dlafb_cholesky_plan_info": (c_int, [c_vp, P_int]),
     "dlafb_cholesky_plan_destroy": (c_int, [c_vp]),
     "dlafb_cholesky_plan_local_size": (c_int, [c_vp, P_i64, P_i64]),
+    "dlafb_cholesky_plan_run_host": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_cholesky_plan_set_profiling": (c_int, [c_vp, c_int]),
     "dlafb_cholesky_plan_profile": (c_int, [c_vp, P_dbl, P_dbl, P_int]),
     "dlafb_cholesky_plan_timeline": (c_int, [c_vp, P_dbl, ctypes.c_longlong]),

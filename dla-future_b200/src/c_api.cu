@@ -123,16 +123,9 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
       pe.dev_bytes = need;
     }
     pe.ldd = ldd;
-    if (rows > 0 && cols > 0 &&
-        cudaMemcpy2DAsync(pe.dev, ldd * es, a, (size_t)d.ld * es, rows * es, cols, cudaMemcpyHostToDevice,
-                          pe.stream) != cudaSuccess)
-      die("host to device copy failed", -1);
-    if ((e = dlafb_cholesky_plan_run(pe.plan, pe.dev, ldd, pe.stream)) != 0)
+    // only the referenced triangle travels, and (uplo = L) finished column panels overlap the remaining steps
+    if ((e = dlafb_cholesky_plan_run_host(pe.plan, a, d.ld, pe.dev, ldd, pe.stream)) != 0)
       die("factorization failed to launch", e);
-    if (rows > 0 && cols > 0 &&
-        cudaMemcpy2DAsync(a, (size_t)d.ld * es, pe.dev, ldd * es, rows * es, cols, cudaMemcpyDeviceToHost,
-                          pe.stream) != cudaSuccess)
-      die("device to host copy failed", -1);
   }
   if ((e = dlafb_cholesky_plan_info(pe.plan, &info)) != 0)
     die("factorization failed", e);

@@ -36,6 +36,7 @@ using namespace dlafb;
 struct dlafb_chol_plan {
   virtual ~dlafb_chol_plan() {}
   virtual int run(void* a, int64_t lda, cudaStream_t stream) = 0;
+  virtual int run_host(void* host, int64_t ldh, void* dev, int64_t ldd, cudaStream_t stream) = 0;
   virtual int info(int* out) = 0;
   virtual void local_size(int64_t* r, int64_t* c) = 0;
   virtual int profile(double* ms, double* flops, int* launches) = 0;
@@ -111,6 +112,11 @@ struct Plan final : dlafb_chol_plan {
   int ib = 64, nblk = 1;
 
   cudaStream_t hp = nullptr, np = nullptr;
+  // host-mirrored runs: finished column panels leave for the host on `dh` while later steps compute
+  cudaStream_t dh = nullptr;
+  cudaEvent_t ev_col = nullptr, ev_dh_end = nullptr;
+  T* sink = nullptr;
+  int64_t sink_ld = 0;
   cudaEvent_t ev_in = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_np[2] = {nullptr, nullptr}, ev_hp_end = nullptr,
               ev_np_end = nullptr;
   T* D = nullptr;  // [inverted diagonal blocks (nblk*ib*ib) | diagonal tile (nb*nb, ld = nb)]
@@ -137,6 +143,9 @@ struct Plan final : dlafb_chol_plan {
     cudaDeviceSynchronize();
     if (hp) cudaStreamDestroy(hp);
     if (np) cudaStreamDestroy(np);
+    if (dh) cudaStreamDestroy(dh);
+    if (ev_col) cudaEventDestroy(ev_col);
+    if (ev_dh_end) cudaEventDestroy(ev_dh_end);
     for (cudaEvent_t e : {ev_in, ev_panel[0], ev_panel[1], ev_np[0], ev_np[1], ev_hp_end, ev_np_end})
       if (e) cudaEventDestroy(e);
     cudaFree(D);
@@ -237,6 +246,9 @@ struct Plan final : dlafb_chol_plan {
     CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CU(cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi));
     CU(cudaStreamCreateWithPriority(&np, cudaStreamNonBlocking, lo));
+    CU(cudaStreamCreateWithFlags(&dh, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ev_col, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_dh_end, cudaEventDisableTiming));
     for (cudaEvent_t* e : {&ev_in, &ev_panel[0], &ev_panel[1], &ev_np[0], &ev_np[1], &ev_hp_end, &ev_np_end})
       CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     CU(cudaMalloc(&info_dev, sizeof(int)));
@@ -348,6 +360,83 @@ struct Plan final : dlafb_chol_plan {
     return (int)launch_gemm_simt<T>(s, p, (unsigned)(count * p.sub * p.sub), 1);
   }
 
+  // column panel k is final on this rank (diagonal tile factored, rows below solved): send it to the host mirror
+  int sink_column(const Step& st, int64_t k, const T* A, int64_t ld) {
+    if (!sink || (dist && !st.in_col))
+      return 0;
+    const int64_t r0 = (st.own_diag ? (int64_t)st.lk_row : (int64_t)st.il0) * nb;
+    const int64_t nrows = mloc - r0, ncols = sched.cols.tile_size(k);
+    if (nrows <= 0 || ncols <= 0)
+      return 0;
+    const size_t c0 = (size_t)st.lk_col * nb;
+    CU(cudaEventRecord(ev_col, hp));
+    CU(cudaStreamWaitEvent(dh, ev_col, 0));
+    CU(cudaMemcpy2DAsync(sink + r0 + c0 * sink_ld, (size_t)sink_ld * sizeof(T), A + r0 + c0 * ld, (size_t)ld * sizeof(T),
+                         (size_t)nrows * sizeof(T), (size_t)ncols, cudaMemcpyDeviceToHost, dh));
+    return 0;
+  }
+
+  // blocks of the referenced triangle of the local matrix in the caller's orientation, one per local tile column
+  template <class F>
+  int for_each_triangle_block(F&& f) const {
+    const Dist1D& crow = upper ? sched.cols : sched.rows;  // caller's rows
+    const Dist1D& ccol = upper ? sched.rows : sched.cols;  // caller's columns
+    const int64_t lrows = crow.local_size(), lcols = ccol.local_size();
+    for (int64_t jl = 0; jl < ccol.nloc_tiles(); ++jl) {
+      const int64_t gj = ccol.global_of(jl);
+      const int64_t c0 = jl * nb, nc = std::min<int64_t>(nb, lcols - c0);
+      int64_t r0, nr;
+      if (!upper) {
+        r0 = crow.next_local(gj) * nb;
+        nr = lrows - r0;
+      }
+      else {
+        r0 = 0;
+        nr = std::min<int64_t>(crow.next_local(gj + 1) * nb, lrows);
+      }
+      if (nr > 0 && nc > 0) {
+        const int e = f(r0, nr, c0, nc);
+        if (e != 0)
+          return e;
+      }
+    }
+    return 0;
+  }
+
+  int run_host(void* host_, int64_t ldh, void* dev_, int64_t ldd, cudaStream_t user) override {
+    T* host = static_cast<T*>(host_);
+    T* dev = static_cast<T*>(dev_);
+    if (n <= 0)
+      return run(dev, ldd, user);
+    int e = for_each_triangle_block([&](int64_t r0, int64_t nr, int64_t c0, int64_t nc) {
+      CU(cudaMemcpy2DAsync(dev + r0 + (size_t)c0 * ldd, (size_t)ldd * sizeof(T), host + r0 + (size_t)c0 * ldh,
+                           (size_t)ldh * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc, cudaMemcpyHostToDevice, user));
+      return 0;
+    });
+    if (e != 0)
+      return e;
+    const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(dev) & 15) || (ldd & 1));
+    const bool overlap = !upper && !misaligned;  // the other cases factor a transposed / realigned copy
+    if (overlap) {
+      sink = host;
+      sink_ld = ldh;
+    }
+    e = run(dev, ldd, user);
+    sink = nullptr;
+    if (e != 0)
+      return e;
+    if (overlap) {
+      CU(cudaEventRecord(ev_dh_end, dh));
+      CU(cudaStreamWaitEvent(user, ev_dh_end, 0));
+      return 0;
+    }
+    return for_each_triangle_block([&](int64_t r0, int64_t nr, int64_t c0, int64_t nc) {
+      CU(cudaMemcpy2DAsync(host + r0 + (size_t)c0 * ldh, (size_t)ldh * sizeof(T), dev + r0 + (size_t)c0 * ldd,
+                           (size_t)ldd * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc, cudaMemcpyDeviceToHost, user));
+      return 0;
+    });
+  }
+
   int factor_lower(T* A, int64_t ld) {
     CUtensorMap map_local[2];  // [0] boxes of 128 rows, [1] of 64 rows
     int nbox_local = 1;
@@ -387,10 +476,18 @@ struct Plan final : dlafb_chol_plan {
       }
       if (mark)
         CU(cudaEventRecord(hev[6 * k + 1], hp));
+      if (last) {
+        const int e = sink_column(st, k, A, ld);
+        if (e != 0)
+          return e;
+      }
       if (!last) {
         if (!dist) {
           const int m_below = (int)(n - (k + 1) * nb);
           CU(trsm_panel<T>(hp, (int)nb, Akk, ld, DW, ib, A + (size_t)(k + 1) * nb + (size_t)k * nb * ld, ld, m_below));
+          const int e = sink_column(st, k, A, ld);
+          if (e != 0)
+            return e;
         }
         else {
           if (st.in_col) {
@@ -407,6 +504,9 @@ struct Plan final : dlafb_chol_plan {
               CU(trsm_panel<T>(hp, (int)nb, Lkk, ldl, DW, ib, B, ld, m_below));
               CU(pack_tiles<T>(hp, m_below, (int)nb, B, ld, Pr[buf] + (size_t)st.il0 * slot, (int)nb));
             }
+            const int e = sink_column(st, k, A, ld);
+            if (e != 0)
+              return e;
           }
           if (mark)
             CU(cudaEventRecord(hev[6 * k + 2], hp));
@@ -565,6 +665,13 @@ int dlafb_cholesky_plan_create(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char 
     case 'z': return create<double2>(plan, grid, uplo, n, nb, src_r, src_c);
   }
   return -1;
+}
+
+int dlafb_cholesky_plan_run_host(dlafb_chol_plan_t plan, void* host, int64_t ldh, void* dev, int64_t ldd,
+                                 void* stream) {
+  if (!plan || !host || !dev)
+    return 1;
+  return plan->run_host(host, ldh, dev, ldd, static_cast<cudaStream_t>(stream));
 }
 
 int dlafb_cholesky_plan_run(dlafb_chol_plan_t plan, void* a, int64_t lda, void* stream) {

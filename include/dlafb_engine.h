@@ -72,6 +72,12 @@ int dlafb_cholesky_plan_create(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char 
  * Asynchronous: work starts after everything already enqueued on `stream` (cudaStream_t) and `stream` waits for
  * the factorization before running anything enqueued later. Collective over the grid. */
 int dlafb_cholesky_plan_run(dlafb_chol_plan_t plan, void* a, int64_t lda, void* stream);
+/* Host-mirrored run (what the reference's C API does with matrix::MatrixMirror, src/c_api/factorization/cholesky.h:48-55):
+ * copies the referenced triangle of the host block `host` (ld `ldh`) into the device mirror `dev` (ld `ldd`, same
+ * local shape, allocated by the caller), factorizes it there and copies the factor back. Only the referenced triangle
+ * travels; for uplo = L every column panel leaves for the host as soon as it is final, overlapping the remaining
+ * steps. Asynchronous on `stream`; `host` should be pinned for the copies to overlap. */
+int dlafb_cholesky_plan_run_host(dlafb_chol_plan_t plan, void* host, int64_t ldh, void* dev, int64_t ldd, void* stream);
 /* Synchronises with the last run and returns its info: 0, or the 1-based global column of the first
  * non-positive pivot (ScaLAPACK p?potrf convention). */
 int dlafb_cholesky_plan_info(dlafb_chol_plan_t plan, int* info);
