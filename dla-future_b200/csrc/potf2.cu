@@ -60,6 +60,9 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
     for (int ia = 0; ia < RA; ++ia)
       acc[ia][ib] = Tr<T>::zero();
   }
+#ifdef DLAFB_EXP_NOLOOP
+  if (bs > 100)
+#endif
 #pragma unroll 2
   for (int l = 0; l < bs; ++l) {
     const T* xp = Xp + l * NMAX;
@@ -85,6 +88,9 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
     for (int ia = 0; ia < RA; ++ia) {
       const int rw = tx + 32 * ia;
       const bool keep = colok && rw < n && ((factor && rw >= col) || (inv && rw < r0));
+#ifdef DLAFB_EXP_NORMW
+      if (bs > 100)
+#endif
       dcol[rw] = Tr<T>::add(dcol[rw], keep ? acc[ia][ib] : Tr<T>::zero());
     }
   }
