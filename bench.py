@@ -234,6 +234,7 @@ def main():
                        "ms": times[-1], "columns": ["start", "potrf", "panel", "row_bcast", "col_bcast", "lookahead",
                                                      "bulk_begin", "bulk_end"], "steps": plan.timeline()}, fh)
     plan.set_profiling(False)
+    exchange = plan.exchange_mode()
     info = plan.info()
     ms = sum(times) / len(times)
     gflops = flops_cholesky(n) / (ms * 1e-3) / 1e9
@@ -314,7 +315,7 @@ def main():
                          "achieved": round(ach, 2) if ach else None, "peak": peak, "unit": "TFLOP/s",
                          "frac": round(ach / peak, 4) if ach else None, "traffic": None,
                          "launches_timed": upd_n, "note": "FP64 DMMA peak: " + peak_src},
-            "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e, "check": check,
+            "clocks": clocks, "gpu_launches": int(launches), "exchange": exchange, "e2e": e2e, "check": check,
             "times_ms": [round(t, 2) for t in times],
         }
         if not args.no_cpu and world == 1:

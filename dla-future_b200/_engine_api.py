@@ -43,6 +43,7 @@ ENGINE_API = {
     "dlafb_cholesky_plan_set_profiling": (c_int, [c_vp, c_int]),
     "dlafb_cholesky_plan_profile": (c_int, [c_vp, P_dbl, P_dbl, P_int]),
     "dlafb_cholesky_plan_timeline": (c_int, [c_vp, P_dbl, ctypes.c_longlong]),
+    "dlafb_cholesky_plan_exchange_mode": (c_int, [c_vp]),
     "dlafb_launch_count": (ctypes.c_uint64, []),
 }
 
@@ -132,6 +133,9 @@ class CholeskyPlan:
         ms, fl, n = ctypes.c_double(), ctypes.c_double(), c_int()
         _ck(self.L.dlafb_cholesky_plan_profile(self.h, ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(n)), "profile")
         return ms.value, fl.value, n.value
+
+    def exchange_mode(self):
+        return {0: "local", 1: "nccl", 2: "p2p"}.get(self.L.dlafb_cholesky_plan_exchange_mode(self.h), "?")
 
     def timeline(self):
         """Rows of 8 times (ms since the start of the last profiled run), one row per step; see dlafb_engine.h."""

@@ -41,6 +41,7 @@ struct dlafb_chol_plan {
   virtual void local_size(int64_t* r, int64_t* c) = 0;
   virtual int profile(double* ms, double* flops, int* launches) = 0;
   virtual int timeline(double* out, long long cap) = 0;
+  virtual int exchange_mode() const = 0;
   bool profiling = false;
 };
 
@@ -48,6 +49,27 @@ namespace {
 
 // launches with fewer 128 x 128 blocks than this use the 64 x 64 shape (148 SMs)
 constexpr size_t kSmallShapeBelow = 120;
+
+// One-thread kernel that publishes a step counter in a peer GPU's memory, ordered after everything that precedes it
+// on its stream (the copies of a panel): the peer's stream waits on it with a stream memory operation, no SM.
+__global__ void flag_write_kernel(volatile uint32_t* flag, uint32_t value) {
+  __threadfence_system();
+  *flag = value;
+  __threadfence_system();
+}
+
+using StreamWaitValue32Fn = CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+StreamWaitValue32Fn stream_wait_value32() {
+  static StreamWaitValue32Fn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<StreamWaitValue32Fn>(f);
+  }();
+  return fn;
+}
 
 // shape of the bulk launches (DLAFB_BULK_SHAPE=0: one 128 x 128 CTA per SM, 3: two 64 x 128 CTAs per SM)
 GemmShape bulk_shape() {
@@ -63,6 +85,12 @@ GemmShape bulk_shape() {
     cudaError_t e_ = (x);        \
     if (e_ != cudaSuccess)       \
       return (int)e_;            \
+  } while (0)
+#define PP(x)                    \
+  do {                           \
+    const int p_ = (x);          \
+    if (p_ != 0)                 \
+      return p_;                 \
   } while (0)
 #define NC(x)                    \
   do {                           \
@@ -120,7 +148,31 @@ struct Plan final : dlafb_chol_plan {
   cudaEvent_t ev_in = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_np[2] = {nullptr, nullptr}, ev_hp_end = nullptr,
               ev_np_end = nullptr;
   T* D = nullptr;  // [inverted diagonal blocks (nblk*ib*ib) | diagonal tile (nb*nb, ld = nb)]
+  T* Dk[2] = {nullptr, nullptr};  // D of even / odd steps (the same buffer unless peers write into it)
   size_t d_elems = 0;
+
+  // ---- panel exchange over NVLink peer memory instead of NCCL (one node, one process per GPU) ----
+  // Every rank owns one arena [flags | D0 D1 | Pr0 Pr1 | Pc0 Pc1] with the same layout everywhere, exported with CUDA
+  // IPC to the ranks of its grid row and column. The owner of a panel COPIES it into the peers' arenas with the copy
+  // engines (side streams, no SM) and then raises a step counter there; the receivers' streams wait for the counter
+  // with cuStreamWaitValue32. Receivers acknowledge "step s consumed" the same way before a buffer is reused.
+  // (ncclBroadcast kept resident, spinning kernels on every receiver: 6 % of the SM time at 8 GPUs.)
+  struct P2P {
+    bool on = false;
+    uint8_t* base = nullptr;
+    size_t bytes = 0, off_D[2] = {0, 0}, off_Pr[2] = {0, 0}, off_Pc[2] = {0, 0};
+    std::vector<uint8_t*> row_peer, col_peer;   // arena of the rank in grid column q / grid row r (self: base)
+    std::vector<cudaStream_t> cs_row, cs_col;   // one copy stream per peer
+    std::vector<cudaEvent_t> ev_row_sent[2], ev_col_sent[2], ev_tail;
+    cudaEvent_t ev_src = nullptr, ev_la = nullptr;
+    uint64_t epoch = 0;  // factorizations run so far: the step counters never restart
+  } pp;
+  uint32_t* flag_at(uint8_t* arena, int idx) const { return reinterpret_cast<uint32_t*>(arena) + idx; }
+  int f_sig_d(int b) const { return b; }
+  int f_sig_row(int b) const { return 2 + b; }
+  int f_sig_col(int b, int r) const { return 4 + b * P + r; }
+  int f_done_row(int q) const { return 4 + 2 * P + q; }
+  int f_done_col(int r) const { return 4 + 2 * P + Q + r; }
   T* Pr[2] = {nullptr, nullptr};  // row panel: one nb x nb slot per local row tile
   T* Pc[2] = {nullptr, nullptr};  // transposed panel: one slot per local column tile
   CUtensorMap map_pr[2], map_pc[2];      // boxes of 128 rows (throughput shape)
@@ -148,11 +200,29 @@ struct Plan final : dlafb_chol_plan {
     if (ev_dh_end) cudaEventDestroy(ev_dh_end);
     for (cudaEvent_t e : {ev_in, ev_panel[0], ev_panel[1], ev_np[0], ev_np[1], ev_hp_end, ev_np_end})
       if (e) cudaEventDestroy(e);
-    cudaFree(D);
+    if (!pp.base)
+      cudaFree(D);
+    for (uint8_t* q : pp.row_peer)
+      if (q && q != pp.base) cudaIpcCloseMemHandle(q);
+    for (uint8_t* q : pp.col_peer)
+      if (q && q != pp.base) cudaIpcCloseMemHandle(q);
+    for (cudaStream_t q : pp.cs_row)
+      if (q) cudaStreamDestroy(q);
+    for (cudaStream_t q : pp.cs_col)
+      if (q) cudaStreamDestroy(q);
     for (int b = 0; b < 2; ++b) {
-      cudaFree(Pr[b]);
-      cudaFree(Pc[b]);
+      for (cudaEvent_t e : pp.ev_row_sent[b]) cudaEventDestroy(e);
+      for (cudaEvent_t e : pp.ev_col_sent[b]) cudaEventDestroy(e);
     }
+    for (cudaEvent_t e : pp.ev_tail) cudaEventDestroy(e);
+    if (pp.ev_src) cudaEventDestroy(pp.ev_src);
+    if (pp.ev_la) cudaEventDestroy(pp.ev_la);
+    if (!pp.base)
+      for (int b = 0; b < 2; ++b) {
+        cudaFree(Pr[b]);
+        cudaFree(Pc[b]);
+      }
+    cudaFree(pp.base);
     cudaFree(lists);
     cudaFree(info_dev);
     cudaFree(tbuf);
@@ -220,6 +290,145 @@ struct Plan final : dlafb_chol_plan {
     *c = upper ? mloc : nloc;
   }
 
+  // Collective over the grid. Falls back to NCCL (pp.on = false) unless EVERY rank could map its peers.
+  int p2p_setup(dlafb_grid* g) {
+    const char* env = getenv("DLAFB_P2P");
+    int ok = (env && env[0] == '0') ? 0 : 1;
+    if (ok && (stream_wait_value32() == nullptr || nt <= 0))
+      ok = 0;
+    // uniform layout: sizes from the largest local tile counts of the grid
+    const size_t slotb = (size_t)nb * nb * sizeof(T);
+    const size_t rt_max = (size_t)((nt + P - 1) / P), ct_max = (size_t)((nt + Q - 1) / Q);
+    auto up = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+    size_t off = up(sizeof(uint32_t) * (size_t)(4 + 3 * P + Q));
+    for (int b = 0; b < 2; ++b) {
+      pp.off_D[b] = off;
+      off += up(d_elems * sizeof(T));
+    }
+    for (int b = 0; b < 2; ++b) {
+      pp.off_Pr[b] = off;
+      off += up((rt_max + 1) * slotb);
+    }
+    for (int b = 0; b < 2; ++b) {
+      pp.off_Pc[b] = off;
+      off += up((ct_max + 1) * slotb);
+    }
+    pp.bytes = off;
+    struct Info {
+      cudaIpcMemHandle_t h;
+      int pr, pc, ok;
+    } mine{};
+    mine.pr = pr;
+    mine.pc = pc;
+    if (ok) {
+      if (cudaMalloc(&pp.base, pp.bytes) != cudaSuccess || cudaMemset(pp.base, 0, pp.bytes) != cudaSuccess ||
+          cudaIpcGetMemHandle(&mine.h, pp.base) != cudaSuccess) {
+        cudaGetLastError();
+        ok = 0;
+      }
+    }
+    mine.ok = ok;
+    // exchange the handles (bytes through the world communicator)
+    const int W = g->world_size;
+    std::vector<Info> all((size_t)W);
+    uint8_t* xbuf = nullptr;
+    CU(cudaMalloc(&xbuf, sizeof(Info) * (size_t)(W + 1)));
+    CU(cudaMemcpy(xbuf, &mine, sizeof(Info), cudaMemcpyHostToDevice));
+    NC(ncclAllGather(xbuf, xbuf + sizeof(Info), sizeof(Info), ncclUint8, g->world, g->stream));
+    CU(cudaStreamSynchronize(g->stream));
+    CU(cudaMemcpy(all.data(), xbuf + sizeof(Info), sizeof(Info) * (size_t)W, cudaMemcpyDeviceToHost));
+    for (const Info& i : all)
+      ok = ok && i.ok;
+    pp.row_peer.assign((size_t)Q, nullptr);
+    pp.col_peer.assign((size_t)P, nullptr);
+    if (ok) {
+      for (const Info& i : all) {
+        const bool same_row = i.pr == pr, same_col = i.pc == pc;
+        if (!same_row && !same_col)
+          continue;
+        uint8_t* ptr = pp.base;
+        if (!(same_row && same_col)) {
+          void* v = nullptr;
+          if (cudaIpcOpenMemHandle(&v, i.h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            ok = 0;
+            break;
+          }
+          ptr = static_cast<uint8_t*>(v);
+        }
+        if (same_row)
+          pp.row_peer[(size_t)i.pc] = ptr;
+        if (same_col)
+          pp.col_peer[(size_t)i.pr] = ptr;
+      }
+    }
+    // second agreement: every rank opened every handle it needs
+    int* flag = reinterpret_cast<int*>(xbuf);
+    CU(cudaMemcpy(flag, &ok, sizeof(int), cudaMemcpyHostToDevice));
+    NC(ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, g->world, g->stream));
+    CU(cudaStreamSynchronize(g->stream));
+    CU(cudaMemcpy(&ok, flag, sizeof(int), cudaMemcpyDeviceToHost));
+    CU(cudaFree(xbuf));
+    if (!ok) {
+      for (uint8_t*& q : pp.row_peer) {
+        if (q && q != pp.base) cudaIpcCloseMemHandle(q);
+        q = nullptr;
+      }
+      for (uint8_t*& q : pp.col_peer) {
+        if (q && q != pp.base) cudaIpcCloseMemHandle(q);
+        q = nullptr;
+      }
+      cudaFree(pp.base);
+      pp.base = nullptr;
+      cudaGetLastError();
+      return 0;  // NCCL path
+    }
+    int lo, hi;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    pp.cs_row.assign((size_t)Q, nullptr);
+    pp.cs_col.assign((size_t)P, nullptr);
+    for (int q = 0; q < Q; ++q)
+      if (q != pc)
+        CU(cudaStreamCreateWithPriority(&pp.cs_row[(size_t)q], cudaStreamNonBlocking, hi));
+    for (int r = 0; r < P; ++r)
+      if (r != pr)
+        CU(cudaStreamCreateWithPriority(&pp.cs_col[(size_t)r], cudaStreamNonBlocking, hi));
+    for (int b = 0; b < 2; ++b) {
+      pp.ev_row_sent[b].resize((size_t)Q);
+      pp.ev_col_sent[b].resize((size_t)P);
+      for (cudaEvent_t& e : pp.ev_row_sent[b])
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      for (cudaEvent_t& e : pp.ev_col_sent[b])
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    pp.ev_tail.resize((size_t)(P + Q));
+    for (cudaEvent_t& e : pp.ev_tail)
+      CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&pp.ev_src, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&pp.ev_la, cudaEventDisableTiming));
+    for (int b = 0; b < 2; ++b) {
+      Dk[b] = reinterpret_cast<T*>(pp.base + pp.off_D[b]);
+      Pr[b] = reinterpret_cast<T*>(pp.base + pp.off_Pr[b]);
+      Pc[b] = reinterpret_cast<T*>(pp.base + pp.off_Pc[b]);
+    }
+    D = Dk[0];
+    pp.on = true;
+    return 0;
+  }
+
+  int exchange_mode() const override { return !dist ? 0 : (pp.on ? 2 : 1); }
+
+  int wait_flag(cudaStream_t s, int idx, uint32_t value) {
+    const CUresult r = stream_wait_value32()(s, reinterpret_cast<CUdeviceptr>(flag_at(pp.base, idx)), value,
+                                             CU_STREAM_WAIT_VALUE_GEQ);
+    return r == CUDA_SUCCESS ? 0 : 1000 + (int)r;
+  }
+  int raise_flag(cudaStream_t s, uint8_t* arena, int idx, uint32_t value) {
+    flag_write_kernel<<<1, 1, 0, s>>>(flag_at(arena, idx), value);
+    ++g_launches;
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+  }
+
   int init(dlafb_grid* g, char uplo, int64_t n_, int64_t nb_, int sr, int sc) {
     upper = (uplo == 'U' || uplo == 'u');
     n = n_;
@@ -254,15 +463,25 @@ struct Plan final : dlafb_chol_plan {
     CU(cudaMalloc(&info_dev, sizeof(int)));
     CU(cudaMemset(info_dev, 0, sizeof(int)));
     d_elems = (size_t)nblk * ib * ib + (size_t)nb * nb;
-    CU(cudaMalloc(&D, d_elems * sizeof(T)));
-    CU(cudaMemset(D, 0, d_elems * sizeof(T)));
+    if (dist) {
+      const int e = p2p_setup(g);
+      if (e != 0)
+        return e;
+    }
+    if (!pp.on) {
+      CU(cudaMalloc(&D, d_elems * sizeof(T)));
+      CU(cudaMemset(D, 0, d_elems * sizeof(T)));
+      Dk[0] = Dk[1] = D;
+    }
     if (dist) {
       const size_t rt = (size_t)sched.rows.nloc_tiles(), ct = (size_t)sched.cols.nloc_tiles();
       for (int b = 0; b < 2; ++b) {
-        CU(cudaMalloc(&Pr[b], (rt + 1) * nb * nb * sizeof(T)));
-        CU(cudaMalloc(&Pc[b], (ct + 1) * nb * nb * sizeof(T)));
-        CU(cudaMemset(Pr[b], 0, (rt + 1) * nb * nb * sizeof(T)));
-        CU(cudaMemset(Pc[b], 0, (ct + 1) * nb * nb * sizeof(T)));
+        if (!pp.on) {
+          CU(cudaMalloc(&Pr[b], (rt + 1) * nb * nb * sizeof(T)));
+          CU(cudaMalloc(&Pc[b], (ct + 1) * nb * nb * sizeof(T)));
+          CU(cudaMemset(Pr[b], 0, (rt + 1) * nb * nb * sizeof(T)));
+          CU(cudaMemset(Pc[b], 0, (ct + 1) * nb * nb * sizeof(T)));
+        }
         if (fast) {
           if (rt && make_operand_map(&map_pr[b], (const double*)Pr[b], (long long)rt * nb, nb, nb, 4) != 0)
             return -2;
@@ -455,15 +674,27 @@ struct Plan final : dlafb_chol_plan {
       if (r != 0)
         return -2;
     }
-    T* DW = D;
-    T* DL = D + (size_t)nblk * ib * ib;
     const ncclDataType_t nt_ = NcclType<T>::t;
     const size_t mult = NcclType<T>::mult;
     const size_t slot = (size_t)nb * nb;
+    const size_t slotb = slot * sizeof(T);
 
     for (int64_t k = 0; k < nt; ++k) {
       const Step& st = sched.steps[k];
       const int buf = (int)(k & 1);
+      T* DW = Dk[buf];
+      T* DL = DW + (size_t)nblk * ib * ib;
+      // global step number: the counters in the peers' arenas never restart (pp.epoch = runs so far)
+      const uint32_t gs = (uint32_t)(pp.epoch * (uint64_t)nt + (uint64_t)k);
+      if (pp.on) {
+        // my copies of step k-2 out of Pr[buf] / Dk[buf] must have left before this step overwrites them
+        for (int q = 0; q < Q; ++q)
+          if (q != pc)
+            CU(cudaStreamWaitEvent(hp, pp.ev_row_sent[buf][(size_t)q], 0));
+        for (int r = 0; r < P; ++r)
+          if (r != pr)
+            CU(cudaStreamWaitEvent(hp, pp.ev_col_sent[buf][(size_t)r], 0));
+      }
       const int nk = (int)sched.rows.tile_size(k);
       const bool last = (k == nt - 1);
       T* Akk = nullptr;
@@ -491,10 +722,29 @@ struct Plan final : dlafb_chol_plan {
         }
         else {
           if (st.in_col) {
-            if (P > 1) {
+            if (P > 1 && !pp.on) {
               if (st.own_diag)
                 CU(lacpy<T>(hp, 'L', (int)nb, (int)nb, Akk, ld, DL, nb));
-              NC(ncclBroadcast(D, D, d_elems * mult, nt_, st.diag_root, colc, hp));
+              NC(ncclBroadcast(DW, DW, d_elems * mult, nt_, st.diag_root, colc, hp));
+            }
+            else if (P > 1 && st.own_diag) {
+              CU(lacpy<T>(hp, 'L', (int)nb, (int)nb, Akk, ld, DL, nb));
+              CU(cudaEventRecord(pp.ev_src, hp));
+              for (int r = 0; r < P; ++r) {
+                if (r == pr)
+                  continue;
+                cudaStream_t cs = pp.cs_col[(size_t)r];
+                CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
+                if (gs >= 2)
+                  PP(wait_flag(cs, f_done_col(r), gs - 1));
+                CU(cudaMemcpyAsync(pp.col_peer[(size_t)r] + pp.off_D[buf], DW, d_elems * sizeof(T),
+                                   cudaMemcpyDeviceToDevice, cs));
+                PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_d(buf), gs + 1));
+                CU(cudaEventRecord(pp.ev_col_sent[buf][(size_t)r], cs));
+              }
+            }
+            else if (P > 1) {
+              PP(wait_flag(hp, f_sig_d(buf), gs + 1));
             }
             const T* Lkk = (P > 1) ? DL : Akk;
             const int64_t ldl = (P > 1) ? nb : ld;
@@ -511,14 +761,66 @@ struct Plan final : dlafb_chol_plan {
           if (mark)
             CU(cudaEventRecord(hev[6 * k + 2], hp));
           const size_t row_cnt = (size_t)(st.il_end - st.il0) * slot;
-          if (Q > 1 && row_cnt > 0) {
+          if (Q > 1 && row_cnt > 0 && !pp.on) {
             T* p = Pr[buf] + (size_t)st.il0 * slot;
             NC(ncclBroadcast(p, p, row_cnt * mult, nt_, st.row_root, rowc, hp));
+          }
+          else if (Q > 1 && row_cnt > 0 && st.in_col) {
+            const size_t o = (size_t)st.il0 * slotb;
+            CU(cudaEventRecord(pp.ev_src, hp));
+            for (int q = 0; q < Q; ++q) {
+              if (q == pc)
+                continue;
+              cudaStream_t cs = pp.cs_row[(size_t)q];
+              CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
+              if (gs >= 2)
+                PP(wait_flag(cs, f_done_row(q), gs - 1));
+              CU(cudaMemcpyAsync(pp.row_peer[(size_t)q] + pp.off_Pr[buf] + o, reinterpret_cast<uint8_t*>(Pr[buf]) + o,
+                                 row_cnt * sizeof(T), cudaMemcpyDeviceToDevice, cs));
+              PP(raise_flag(cs, pp.row_peer[(size_t)q], f_sig_row(buf), gs + 1));
+              CU(cudaEventRecord(pp.ev_row_sent[buf][(size_t)q], cs));
+            }
+          }
+          else if (Q > 1 && row_cnt > 0) {
+            PP(wait_flag(hp, f_sig_row(buf), gs + 1));
           }
           if (mark)
             CU(cudaEventRecord(hev[6 * k + 3], hp));
           if (!st.colb.empty()) {
-            if (P > 1) {
+            if (P > 1 && pp.on) {
+              // every rank row forwards the tiles whose diagonal position it owns, straight into the peers' Pc
+              bool sends = false;
+              std::vector<char> from((size_t)P, 0);
+              for (const ColBcast& cb : st.colb) {
+                from[(size_t)cb.root] = 1;
+                if (cb.root == pr) {
+                  sends = true;
+                  CU(cudaMemcpyAsync(Pc[buf] + (size_t)cb.jl * slot, Pr[buf] + (size_t)cb.src_il * slot, slotb,
+                                     cudaMemcpyDeviceToDevice, hp));
+                }
+              }
+              if (sends) {
+                CU(cudaEventRecord(pp.ev_src, hp));
+                for (int r = 0; r < P; ++r) {
+                  if (r == pr)
+                    continue;
+                  cudaStream_t cs = pp.cs_col[(size_t)r];
+                  CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
+                  if (gs >= 2)
+                    PP(wait_flag(cs, f_done_col(r), gs - 1));
+                  for (const ColBcast& cb : st.colb)
+                    if (cb.root == pr)
+                      CU(cudaMemcpyAsync(pp.col_peer[(size_t)r] + pp.off_Pc[buf] + (size_t)cb.jl * slotb,
+                                         Pr[buf] + (size_t)cb.src_il * slot, slotb, cudaMemcpyDeviceToDevice, cs));
+                  PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_col(buf, pr), gs + 1));
+                  CU(cudaEventRecord(pp.ev_col_sent[buf][(size_t)r], cs));
+                }
+              }
+              for (int r = 0; r < P; ++r)
+                if (r != pr && from[(size_t)r])
+                  PP(wait_flag(hp, f_sig_col(buf, r), gs + 1));
+            }
+            else if (P > 1) {
               NC(ncclGroupStart());
               for (const ColBcast& cb : st.colb) {
                 T* recv = Pc[buf] + (size_t)cb.jl * slot;
@@ -563,6 +865,38 @@ struct Plan final : dlafb_chol_plan {
         np_timed[k] = timed;
         CU(cudaEventRecord(ev_np[buf], np));
       }
+      if (pp.on) {
+        // "step k consumed here": after the look-ahead update, the bulk update and my forwarding copies of this step
+        CU(cudaEventRecord(pp.ev_la, hp));
+        CU(cudaStreamWaitEvent(np, pp.ev_la, 0));
+        for (int q = 0; q < Q; ++q)
+          if (q != pc)
+            CU(cudaStreamWaitEvent(np, pp.ev_row_sent[buf][(size_t)q], 0));
+        for (int r = 0; r < P; ++r)
+          if (r != pr)
+            CU(cudaStreamWaitEvent(np, pp.ev_col_sent[buf][(size_t)r], 0));
+        for (int q = 0; q < Q; ++q)
+          if (q != pc)
+            PP(raise_flag(np, pp.row_peer[(size_t)q], f_done_row(pc), gs + 1));
+        for (int r = 0; r < P; ++r)
+          if (r != pr)
+            PP(raise_flag(np, pp.col_peer[(size_t)r], f_done_col(pr), gs + 1));
+      }
+    }
+    if (pp.on) {
+      // the side streams end before the run does
+      size_t i = 0;
+      for (cudaStream_t cs : pp.cs_row)
+        if (cs) {
+          CU(cudaEventRecord(pp.ev_tail[i], cs));
+          CU(cudaStreamWaitEvent(hp, pp.ev_tail[i++], 0));
+        }
+      for (cudaStream_t cs : pp.cs_col)
+        if (cs) {
+          CU(cudaEventRecord(pp.ev_tail[i], cs));
+          CU(cudaStreamWaitEvent(hp, pp.ev_tail[i++], 0));
+        }
+      ++pp.epoch;
     }
     return 0;
   }
@@ -691,6 +1025,10 @@ int dlafb_cholesky_plan_set_profiling(dlafb_chol_plan_t plan, int on) {
     return -1;
   plan->profiling = on != 0;
   return 0;
+}
+
+int dlafb_cholesky_plan_exchange_mode(dlafb_chol_plan_t plan) {
+  return plan ? plan->exchange_mode() : -1;
 }
 
 int dlafb_cholesky_plan_timeline(dlafb_chol_plan_t plan, double* out, long long cap) {

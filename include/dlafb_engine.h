@@ -94,6 +94,11 @@ int dlafb_cholesky_plan_profile(dlafb_chol_plan_t plan, double* update_ms, doubl
  * updated (all on the high-priority stream), bulk update begin / end. -1 where not recorded. out holds >= 8*nt. */
 int dlafb_cholesky_plan_timeline(dlafb_chol_plan_t plan, double* out, long long cap);
 
+/* How the panels travel between ranks: 0 = single rank, 1 = ncclBroadcast on row / column communicators,
+ * 2 = copies into the peers' memory over NVLink (CUDA IPC, copy engines) with stream-ordered step counters; chosen at
+ * plan creation (2 when every rank of the grid can map its row and column peers; DLAFB_P2P=0 forces 1). */
+int dlafb_cholesky_plan_exchange_mode(dlafb_chol_plan_t plan);
+
 /* Kernels launched by this library so far in this process. */
 uint64_t dlafb_launch_count(void);
 
