@@ -140,6 +140,11 @@ struct Plan final : dlafb_chol_plan {
   int ib = 64, nblk = 1;
 
   cudaStream_t hp = nullptr, np = nullptr;
+  // diagonal tile k+1 is factored on its own stream as soon as ITS look-ahead update is done, next to the look-ahead
+  // update of the rest of column k+1 (both are on the critical path of step k+1)
+  cudaStream_t dp = nullptr;
+  cudaEvent_t ev_ladiag = nullptr, ev_potrf = nullptr;
+  bool diag_ahead = false;  // ev_ladiag of the previous step covers this step's diagonal tile
   // host-mirrored runs: finished column panels leave for the host on `dh` while later steps compute
   cudaStream_t dh = nullptr;
   cudaEvent_t ev_col = nullptr, ev_dh_end = nullptr;
@@ -195,6 +200,9 @@ struct Plan final : dlafb_chol_plan {
     cudaDeviceSynchronize();
     if (hp) cudaStreamDestroy(hp);
     if (np) cudaStreamDestroy(np);
+    if (dp) cudaStreamDestroy(dp);
+    if (ev_ladiag) cudaEventDestroy(ev_ladiag);
+    if (ev_potrf) cudaEventDestroy(ev_potrf);
     if (dh) cudaStreamDestroy(dh);
     if (ev_col) cudaEventDestroy(ev_col);
     if (ev_dh_end) cudaEventDestroy(ev_dh_end);
@@ -455,6 +463,9 @@ struct Plan final : dlafb_chol_plan {
     CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CU(cudaStreamCreateWithPriority(&hp, cudaStreamNonBlocking, hi));
     CU(cudaStreamCreateWithPriority(&np, cudaStreamNonBlocking, lo));
+    CU(cudaStreamCreateWithPriority(&dp, cudaStreamNonBlocking, hi));
+    CU(cudaEventCreateWithFlags(&ev_ladiag, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ev_potrf, cudaEventDisableTiming));
     CU(cudaStreamCreateWithFlags(&dh, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&ev_col, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&ev_dh_end, cudaEventDisableTiming));
@@ -678,6 +689,7 @@ struct Plan final : dlafb_chol_plan {
     const size_t mult = NcclType<T>::mult;
     const size_t slot = (size_t)nb * nb;
     const size_t slotb = slot * sizeof(T);
+    diag_ahead = false;
 
     for (int64_t k = 0; k < nt; ++k) {
       const Step& st = sched.steps[k];
@@ -703,8 +715,19 @@ struct Plan final : dlafb_chol_plan {
         CU(cudaEventRecord(hev[6 * k + 0], hp));
       if (st.own_diag) {
         Akk = A + (size_t)st.lk_row * nb + (size_t)st.lk_col * nb * ld;
-        CU(potrf_tile<T>(hp, 'L', nk, Akk, ld, DW, ib, info_dev, (int)(k * nb)));
+        if (diag_ahead) {
+          // the tile got its last update first thing in the previous step's look-ahead: factor it on `dp` while `hp`
+          // still updates the rest of this column
+          CU(cudaStreamWaitEvent(dp, ev_ladiag, 0));
+          CU(potrf_tile<T>(dp, 'L', nk, Akk, ld, DW, ib, info_dev, (int)(k * nb)));
+          CU(cudaEventRecord(ev_potrf, dp));
+          CU(cudaStreamWaitEvent(hp, ev_potrf, 0));
+        }
+        else {
+          CU(potrf_tile<T>(hp, 'L', nk, Akk, ld, DW, ib, info_dev, (int)(k * nb)));
+        }
       }
+      diag_ahead = false;
       if (mark)
         CU(cudaEventRecord(hev[6 * k + 1], hp));
       if (last) {
@@ -847,7 +870,19 @@ struct Plan final : dlafb_chol_plan {
         // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
         if (k >= 1)
           CU(cudaStreamWaitEvent(hp, ev_np[(k - 1) & 1], 0));
-        int r = update(hp, A, ld, map_local, nbox_local, k, buf, hp_off[k], np_off[k] - hp_off[k]);
+        int r = 0;
+        size_t la_off = hp_off[k], la_cnt = np_off[k] - hp_off[k];
+        if (la_cnt > 0 && st.hp.front().diag) {
+          // this rank owns A(k+1,k+1): its update goes first and releases the factorization of step k+1
+          r = update(hp, A, ld, map_local, nbox_local, k, buf, la_off, 1);
+          if (r != 0)
+            return r;
+          CU(cudaEventRecord(ev_ladiag, hp));
+          diag_ahead = true;
+          ++la_off;
+          --la_cnt;
+        }
+        r = update(hp, A, ld, map_local, nbox_local, k, buf, la_off, la_cnt);
         if (r != 0)
           return r;
         if (mark)
