@@ -93,15 +93,16 @@ __device__ __forceinline__ bool decode_block(const GemmParams& p, int id, BlockC
     const int item = id / nsub;
     const int s = id - item * nsub;
     const int2 it = p.list[item];
+    const int ir = it.x * p.list_scale, ic = (it.y & 0x7fffffff) * p.list_scale;  // list entries are in elements of T
     c.lower = it.y < 0;
     c.trow = (s % sub_m) * BM;
     c.tcol = (s / sub_m) * BN;
-    c.row0 = it.x + c.trow;
-    c.col0 = (it.y & 0x7fffffff) + c.tcol;
+    c.row0 = ir + c.trow;
+    c.col0 = ic + c.tcol;
     c.b_from_a = c.lower;
-    c.b_row_a = it.x + c.tcol + p.a_row_off;
-    c.m_lim = min(c.m_lim, it.x + p.tile);
-    c.n_lim = min(c.n_lim, (it.y & 0x7fffffff) + p.tile);
+    c.b_row_a = ir + c.tcol + p.a_row_off;
+    c.m_lim = min(c.m_lim, ir + p.tile);
+    c.n_lim = min(c.n_lim, ic + p.tile);
   }
   else {
     const int by = id / p.rect_nx;
@@ -118,7 +119,14 @@ __device__ __forceinline__ bool decode_block(const GemmParams& p, int id, BlockC
   return true;
 }
 
-template <int BM, int BN, int STAGES, int MINB>
+// CPLX: the operands are the REAL VIEWS of complex<double> matrices (re/im interleaved along the rows: 2m x K doubles,
+// leading dimension 2*ld), so the same main loop forms the four real products of C = A * B^H at once:
+//   P[2i][2j] = Ar.Br   P[2i][2j+1] = Ar.Bi   P[2i+1][2j] = Ai.Br   P[2i+1][2j+1] = Ai.Bi
+// and the epilogue folds them: Cr = P[2i][2j] + P[2i+1][2j+1], Ci = P[2i+1][2j] - P[2i][2j+1]. In the DMMA fragment
+// a lane holds P[r][2kk], P[r][2kk+1]; its partner row r^1 is lane^4: one shuffle per fragment. All coordinates in
+// GemmParams are in real-view units (rows and product columns doubled); C is addressed as its real view
+// (2m rows, n columns, leading dimension p.ldc doubles).
+template <int BM, int BN, int STAGES, int MINB, bool CPLX>
 __global__ void __launch_bounds__(kGemmThreads, MINB)
     gemm_nt_dmma_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                         const GemmParams p) {
@@ -283,6 +291,61 @@ __global__ void __launch_bounds__(kGemmThreads, MINB)
     const double alpha = p.alpha, beta = p.beta;
     const bool full_block = !c.lower || (c.trow >= c.tcol + BN - 1);
     const long long ldc = p.ldc;
+    if constexpr (CPLX) {
+      // fold the four real products; this lane then owns ONE double per fragment: real-view row rr of C (even: real
+      // part, odd: imaginary part of complex row rr/2), complex column (col0 + cl)/2
+      const double sgn = (r & 1) ? -1.0 : 1.0;
+      double* c00 = p.C + (long long)(col0 >> 1) * ldc + row0;
+      const bool interior = full_block && row0 + BM <= m_lim && col0 + BN <= n_lim;
+      if (interior && beta == 1.0 && (reinterpret_cast<uintptr_t>(c00) & 15) == 0 && (ldc & 1) == 0) {
+        if (stg_pending && threadIdx.x < BN / 2)
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncthreads();  // staging buffer free
+        const uint32_t mine = stg + (wn * (BN / 8) + kk) * kColStride + (wm * (BM / 2) + r) * 8;
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+          for (int f = 0; f < F; ++f) {
+            const double other = __shfl_xor_sync(0xffffffffu, acc[f][g][1], 4);
+            sts_f64(mine + (g * 4) * kColStride + f * 64, alpha * fma(sgn, other, acc[f][g][0]));
+          }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < BN / 2) {
+          double* gp = c00 + (long long)threadIdx.x * ldc;
+          asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;" ::"l"(gp),
+                       "r"(stg + threadIdx.x * kColStride), "r"(BM * 8)
+                       : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        stg_pending = true;
+        continue;
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const int cl = wn * (BN / 4) + g * 8 + 2 * kk;  // product column (even) inside the CTA block
+        const int cc = (col0 + cl) >> 1;               // complex column of C
+        double* colp = p.C + (long long)cc * ldc;
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+          const double other = __shfl_xor_sync(0xffffffffu, acc[f][g][1], 4);  // all lanes take part
+          const int rl = wm * (BM / 2) + f * 8 + r;
+          const int rr = row0 + rl;
+          if (col0 + cl >= n_lim || rr >= m_lim)
+            continue;
+          const int ci = (c.trow + rl) >> 1, cj = (c.tcol + cl) >> 1;  // complex position inside the tile / rectangle
+          if (!full_block && ci < cj)
+            continue;
+          double v = alpha * fma(sgn, other, acc[f][g][0]);
+          if (beta != 0.0)
+            v = fma(beta, colp[rr], v);
+          if (c.lower && ci == cj && (rr & 1))
+            v = 0.0;  // HERK: the diagonal stays real
+          colp[rr] = v;
+        }
+      }
+      continue;
+    }
     if (full_block && row0 + BM <= m_lim && col0 + BN <= n_lim) {
       double* c00 = p.C + (long long)col0 * ldc + row0;
       if (beta == 1.0 && (reinterpret_cast<uintptr_t>(c00) & 15) == 0 && (ldc & 1) == 0) {
@@ -402,7 +465,7 @@ EncodeTiledFn encode_fn() {
 }  // namespace
 
 int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
-                     int kind, int box_rows) {
+                     int kind, int box_rows, long long tile_cols) {
   const cuuint32_t groups = (cuuint32_t)(box_rows / 16);
   EncodeTiledFn enc = encode_fn();
   if (!enc)
@@ -420,10 +483,10 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   }
   else if (kind == 4) {
-    // tile layout (contiguous ld x ld tiles, ld = tile size): rows = number of tiles * ld, cols = ld
-    const cuuint64_t nb = (cuuint64_t)ld;
-    cuuint64_t dims[4] = {16, nb, nb / 16, (cuuint64_t)(rows / ld)};
-    cuuint64_t strides[3] = {nb * 8, 128, nb * nb * 8};
+    // tile layout (contiguous tiles of ld rows x tile_cols columns, leading dimension ld): rows = tiles * ld
+    const cuuint64_t tr = (cuuint64_t)ld, tc = (cuuint64_t)(tile_cols > 0 ? tile_cols : ld);
+    cuuint64_t dims[4] = {16, tc, tr / 16, (cuuint64_t)(rows / ld)};
+    cuuint64_t strides[3] = {tr * 8, 128, tr * tc * 8};
     cuuint32_t box[4] = {16, (cuuint32_t)kBK, groups, 1};
     cuuint32_t es[4] = {1, 1, 1, 1};
     r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<double*>(base), dims, strides, box, es,
@@ -454,12 +517,12 @@ int sm_count() {
   return n;
 }
 
-template <int BM, int BN, int STAGES, int MINB>
+template <int BM, int BN, int STAGES, int MINB, bool CPLX>
 cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b, GemmParams p,
                          unsigned nx, unsigned ny) {
   constexpr int smem = gemm_smem_bytes(BM, BN, STAGES);
   static_assert(MINB * (smem + 1024) <= 228 * 1024, "MINB CTAs must fit the SM's shared memory");
-  static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN, STAGES, MINB>,
+  static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN, STAGES, MINB, CPLX>,
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (attr != cudaSuccess)
     return attr;
@@ -475,26 +538,33 @@ cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CU
   unsigned grid = (unsigned)p.ntiles;
   if (persistent)
     grid = std::min<unsigned>(grid, (unsigned)sm_count() * MINB);
-  gemm_nt_dmma_kernel<BM, BN, STAGES, MINB><<<grid, kGemmThreads, smem, stream>>>(map_a, map_b, p);
+  if (p.list_scale < 1)
+    p.list_scale = 1;
+  gemm_nt_dmma_kernel<BM, BN, STAGES, MINB, CPLX><<<grid, kGemmThreads, smem, stream>>>(map_a, map_b, p);
   ++g_launches;
   return cudaGetLastError();
 }
 }  // namespace
 
 cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
-                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y, GemmShape shape) {
+                                const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y, GemmShape shape,
+                                bool cplx) {
   if (nblocks_x == 0 || nblocks_y == 0)
     return cudaSuccess;
+#define DLAFB_SHAPE(BM, BN, ST, MB)                                                                  \
+  return cplx ? launch_shape<BM, BN, ST, MB, true>(stream, map_a, map_b, p, nblocks_x, nblocks_y)    \
+              : launch_shape<BM, BN, ST, MB, false>(stream, map_a, map_b, p, nblocks_x, nblocks_y)
   switch (shape) {
     case GemmShape::k128x128:
-      return launch_shape<128, 128, 4, 1>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      DLAFB_SHAPE(128, 128, 4, 1);
     case GemmShape::k64x64:
-      return launch_shape<64, 64, 4, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      DLAFB_SHAPE(64, 64, 4, 2);
     case GemmShape::k32x128:
-      return launch_shape<32, 128, 4, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      DLAFB_SHAPE(32, 128, 4, 2);
     case GemmShape::k64x128:
-      return launch_shape<64, 128, 3, 2>(stream, map_a, map_b, p, nblocks_x, nblocks_y);
+      DLAFB_SHAPE(64, 128, 3, 2);
   }
+#undef DLAFB_SHAPE
   return cudaErrorInvalidValue;
 }
 

@@ -57,6 +57,7 @@ struct GemmParams {
   int rect_row0, rect_col0;
   int lower;
   int ntiles, rect_nx;  // filled by the launcher: number of blocks, blocks per rectangle row
+  int list_scale;       // 2 for the real view of complex<double> (list entries count complex elements), else 1
   // 1: rank-3 map (one TMA per operand slice), 8: rank-2 map (one TMA per 16-row group),
   // 4: rank-4 map of a panel stored as contiguous tile x tile tiles (one TMA per slice)
   int nbox_a, nbox_b;
@@ -67,12 +68,14 @@ struct GemmParams {
 // rank-2 view with 16 x 16 boxes; kind 4: panel in tile layout (rows = ntiles*ld, ld = tile size, cols = ld).
 // Returns 0 on success.
 // box_rows = rows of the operand one CTA loads per slice (BM for the A map, BN for the B map of the shape used).
+// kind 4: tiles of ld rows x tile_cols columns (tile_cols = 0: square). For complex<double> pass the real view:
+// rows and ld doubled.
 int make_operand_map(CUtensorMap* map, const double* base, long long rows, long long cols, long long ld,
-                     int kind, int box_rows = 128);
+                     int kind, int box_rows = 128, long long tile_cols = 0);
 
 // Launches the kernel for `nblocks_x` x `nblocks_y` CTAs on `stream`. The maps' boxes must match `shape`.
 cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
                                 const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y,
-                                GemmShape shape = GemmShape::k128x128);
+                                GemmShape shape = GemmShape::k128x128, bool cplx = false);
 
 }  // namespace dlafb

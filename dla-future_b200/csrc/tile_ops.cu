@@ -23,10 +23,17 @@ bool dmma_ok<double>(int M, int N, const double* A, long long lda, const double*
   return M >= 1 && N >= 1 && K > 0 && (K % kBK) == 0 && aligned16(A) && aligned16(B) && (lda % 2) == 0 &&
          (ldb % 2) == 0;
 }
+template <>
+bool dmma_ok<double2>(int M, int N, const double2* A, long long, const double2* B, long long, int K) {
+  // the real view (2M x K doubles, leading dimension 2*lda) is always 16-byte aligned with an even leading dimension
+  return M >= 1 && N >= 1 && K > 0 && (K % kBK) == 0 && aligned16(A) && aligned16(B) && M < (1 << 29) && N < (1 << 29);
+}
 
+// cplx: A, B, C are the real views of complex<double> matrices; M, N, lda, ldb, ldc already doubled by the caller
+// (C: 2M rows x N/2 columns of complex elements = N product columns).
 cudaError_t gemm_nt_dmma_rect(cudaStream_t stream, int M, int N, int K, double alpha, const double* A, long long lda,
                               const double* B, long long ldb, double beta, double* C, long long ldc, int lower,
-                              bool inplace) {
+                              bool inplace, bool cplx = false) {
   // few blocks = a launch whose duration is one CTA's serial chain of K/16 slices: use 4x more, smaller CTAs
   // (the in-place product needs all N <= 128 columns in one CTA, so it splits the rows only)
   const bool small = ceil_div(M, kBM) * ceil_div(N, kBN) < 120;
@@ -57,7 +64,8 @@ cudaError_t gemm_nt_dmma_rect(cudaStream_t stream, int M, int N, int K, double a
   p.lower = lower;
   p.nbox_a = ka == 3 ? 1 : 8;
   p.nbox_b = kb == 3 ? 1 : 8;
-  return launch_gemm_nt_dmma(stream, ma, mb, p, ceil_div(M, bm), ceil_div(N, bn), shape);
+  p.list_scale = 1;
+  return launch_gemm_nt_dmma(stream, ma, mb, p, ceil_div(M, bm), ceil_div(N, bn), shape, cplx);
 }
 
 template <class T>
@@ -72,6 +80,15 @@ cudaError_t gemm_nt_dmma_try<double>(cudaStream_t s, int M, int N, int K, double
   return gemm_nt_dmma_rect(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower, inplace);
 }
 
+template <>
+cudaError_t gemm_nt_dmma_try<double2>(cudaStream_t s, int M, int N, int K, double alpha, const double2* A, long long lda,
+                                      const double2* B, long long ldb, double beta, double2* C, long long ldc,
+                                      int lower, bool inplace) {
+  return gemm_nt_dmma_rect(s, 2 * M, 2 * N, K, alpha, reinterpret_cast<const double*>(A), 2 * lda,
+                           reinterpret_cast<const double*>(B), 2 * ldb, beta, reinterpret_cast<double*>(C), 2 * ldc,
+                           lower, inplace, true);
+}
+
 }  // namespace
 
 template <class T>
@@ -81,7 +98,7 @@ cudaError_t gemm_nt(cudaStream_t stream, int M, int N, int K, typename Tr<T>::Re
     return cudaSuccess;
   const bool inplace = static_cast<const void*>(A) == static_cast<const void*>(C);
   if (dmma_ok<T>(M, N, A, lda, B, ldb, K)) {
-    if (inplace && N > kBN)
+    if (inplace && N * (Tr<T>::is_complex ? 2 : 1) > kBN)
       return cudaErrorInvalidValue;
     return gemm_nt_dmma_try<T>(stream, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower, inplace);
   }

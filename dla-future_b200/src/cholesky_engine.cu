@@ -136,7 +136,9 @@ struct Plan final : dlafb_chol_plan {
   Schedule sched;
   int64_t nt = 0, mloc = 0, nloc = 0;  // local rows / cols (L orientation)
   bool dist = false;                   // more than one rank
-  bool fast = false;                   // TMA + DMMA path (double, nb % 128 == 0)
+  bool fast = false;                   // TMA + DMMA path (double with nb % 128 == 0, complex<double> with nb % 64 == 0)
+  bool cplx = false;                   // T is complex<double>: the DMMA kernel works on the real views
+  int vs = 1;                          // doubles per element along a column of the view (2 for complex<double>)
   int ib = 64, nblk = 1;
 
   cudaStream_t hp = nullptr, np = nullptr;
@@ -455,8 +457,11 @@ struct Plan final : dlafb_chol_plan {
     nt = sched.rows.nt();
     mloc = sched.rows.local_size();
     nloc = sched.cols.local_size();
-    fast = std::is_same<T, double>::value && (nb % 128 == 0);
-    ib = fast ? 128 : 64;
+    // DMMA path: double, and complex<double> through its real view (2*nb rows per tile must be a multiple of 128)
+    cplx = std::is_same<T, double2>::value;
+    vs = cplx ? 2 : 1;
+    fast = (std::is_same<T, double>::value && (nb % 128 == 0)) || (cplx && (nb % 64 == 0));
+    ib = (fast && !cplx) ? 128 : 64;
     nblk = (int)((nb + ib - 1) / ib);
 
     int lo, hi;
@@ -494,13 +499,14 @@ struct Plan final : dlafb_chol_plan {
           CU(cudaMemset(Pc[b], 0, (ct + 1) * nb * nb * sizeof(T)));
         }
         if (fast) {
-          if (rt && make_operand_map(&map_pr[b], (const double*)Pr[b], (long long)rt * nb, nb, nb, 4) != 0)
+          const long long tr = (long long)nb * vs;  // rows of a tile in the (real) view
+          if (rt && make_operand_map(&map_pr[b], (const double*)Pr[b], (long long)rt * tr, nb, tr, 4, 128, nb) != 0)
             return -2;
-          if (ct && make_operand_map(&map_pc[b], (const double*)Pc[b], (long long)ct * nb, nb, nb, 4) != 0)
+          if (ct && make_operand_map(&map_pc[b], (const double*)Pc[b], (long long)ct * tr, nb, tr, 4, 128, nb) != 0)
             return -2;
-          if (rt && make_operand_map(&map_pr_s[b], (const double*)Pr[b], (long long)rt * nb, nb, nb, 4, 64) != 0)
+          if (rt && make_operand_map(&map_pr_s[b], (const double*)Pr[b], (long long)rt * tr, nb, tr, 4, 64, nb) != 0)
             return -2;
-          if (ct && make_operand_map(&map_pc_s[b], (const double*)Pc[b], (long long)ct * nb, nb, nb, 4, 64) != 0)
+          if (ct && make_operand_map(&map_pc_s[b], (const double*)Pc[b], (long long)ct * tr, nb, tr, 4, 64, nb) != 0)
             return -2;
         }
       }
@@ -544,26 +550,28 @@ struct Plan final : dlafb_chol_plan {
     if (fast) {
       GemmParams p{};
       p.C = reinterpret_cast<double*>(A);
-      p.ldc = ld;
-      p.m_total = (int)mloc;
-      p.n_total = (int)nloc;
+      p.ldc = ld * vs;
+      p.m_total = (int)(mloc * vs);
+      p.n_total = (int)(nloc * vs);
       p.K = (int)nb;
       p.alpha = -1.0;
       p.beta = 1.0;
       p.list = lists + off;
-      p.tile = (int)nb;
-      const size_t big = count * (nb / 128) * (nb / 128);
+      p.tile = (int)(nb * vs);
+      p.list_scale = vs;
+      const size_t big = count * (p.tile / 128) * (p.tile / 128);
       const GemmShape shape = big < kSmallShapeBelow ? GemmShape::k64x64 : bulk_shape();
       const int bm = shape_bm(shape), bn = shape_bn(shape);
-      const unsigned ctas = (unsigned)(count * (nb / bm) * (nb / bn));
+      const unsigned ctas = (unsigned)(count * (p.tile / bm) * (p.tile / bn));
       if (dist) {
         p.nbox_a = p.nbox_b = 4;
         return (int)launch_gemm_nt_dmma(s, bm == 64 ? map_pr_s[buf] : map_pr[buf], bn == 64 ? map_pc_s[buf] : map_pc[buf],
-                                        p, ctas, 1, shape);
+                                        p, ctas, 1, shape, cplx);
       }
       p.a_col0 = p.b_col0 = (int)(k * nb);
       p.nbox_a = p.nbox_b = nbox_local;
-      return (int)launch_gemm_nt_dmma(s, map_a_local[bm == 64 ? 1 : 0], map_a_local[bn == 64 ? 1 : 0], p, ctas, 1, shape);
+      return (int)launch_gemm_nt_dmma(s, map_a_local[bm == 64 ? 1 : 0], map_a_local[bn == 64 ? 1 : 0], p, ctas, 1, shape,
+                                      cplx);
     }
     SimtParams<T> p{};
     p.C = A;
@@ -645,7 +653,7 @@ struct Plan final : dlafb_chol_plan {
     });
     if (e != 0)
       return e;
-    const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(dev) & 15) || (ldd & 1));
+    const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(dev) & 15) || ((ldd * vs) & 1));
     const bool overlap = !upper && !misaligned;  // the other cases factor a transposed / realigned copy
     if (overlap) {
       sink = host;
@@ -672,13 +680,14 @@ struct Plan final : dlafb_chol_plan {
     int nbox_local = 1;
     if (fast && !dist && n > 0) {
       // rank-3 view reads whole 16-row groups: fine when the rows are a multiple of 16 or the columns are padded
-      const int kind = (mloc % 16 == 0 || ld >= round_up(mloc, 16)) ? 3 : 2;
-      int r = make_operand_map(&map_local[0], (const double*)A, mloc, nloc, ld, kind);
+      const long long vr = mloc * vs, vld = ld * vs;  // the (real) view
+      const int kind = (vr % 16 == 0 || vld >= round_up(vr, 16)) ? 3 : 2;
+      int r = make_operand_map(&map_local[0], (const double*)A, vr, nloc, vld, kind);
       if (r == 0)
-        r = make_operand_map(&map_local[1], (const double*)A, mloc, nloc, ld, kind, 64);
+        r = make_operand_map(&map_local[1], (const double*)A, vr, nloc, vld, kind, 64);
       nbox_local = kind == 3 ? 1 : 8;
       if (r != 0 && kind == 3) {
-        r = make_operand_map(&map_local[0], (const double*)A, mloc, nloc, ld, 2);
+        r = make_operand_map(&map_local[0], (const double*)A, vr, nloc, vld, 2);
         map_local[1] = map_local[0];
         nbox_local = 8;
       }
@@ -959,7 +968,7 @@ struct Plan final : dlafb_chol_plan {
     int r = 0;
     if (n > 0) {
       if (!upper) {
-        const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(a) & 15) || (lda & 1));
+        const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(a) & 15) || ((lda * vs) & 1));
         if (misaligned) {
           if (!tbuf) {
             ldt = round_up(mloc > 0 ? mloc : 1, 64);
