@@ -506,7 +506,7 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
 }
 
 namespace {
-int sm_count() {
+int sm_count_impl() {
   static int n = [] {
     int dev = 0, v = 0;
     if (cudaGetDevice(&dev) != cudaSuccess ||
@@ -519,7 +519,7 @@ int sm_count() {
 
 template <int BM, int BN, int STAGES, int MINB, bool CPLX>
 cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b, GemmParams p,
-                         unsigned nx, unsigned ny) {
+                         unsigned nx, unsigned ny, unsigned max_ctas) {
   constexpr int smem = gemm_smem_bytes(BM, BN, STAGES);
   static_assert(MINB * (smem + 1024) <= 228 * 1024, "MINB CTAs must fit the SM's shared memory");
   static cudaError_t attr = cudaFuncSetAttribute(gemm_nt_dmma_kernel<BM, BN, STAGES, MINB, CPLX>,
@@ -537,7 +537,9 @@ cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CU
   }();
   unsigned grid = (unsigned)p.ntiles;
   if (persistent)
-    grid = std::min<unsigned>(grid, (unsigned)sm_count() * MINB);
+    grid = std::min<unsigned>(grid, (unsigned)sm_count_impl() * MINB);
+  if (max_ctas > 0)
+    grid = std::min<unsigned>(grid, max_ctas);  // persistent on purpose: the caller keeps SM slots free
   if (p.list_scale < 1)
     p.list_scale = 1;
   gemm_nt_dmma_kernel<BM, BN, STAGES, MINB, CPLX><<<grid, kGemmThreads, smem, stream>>>(map_a, map_b, p);
@@ -546,14 +548,18 @@ cudaError_t launch_shape(cudaStream_t stream, const CUtensorMap& map_a, const CU
 }
 }  // namespace
 
+int gemm_sm_count() {
+  return sm_count_impl();
+}
+
 cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
                                 const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y, GemmShape shape,
-                                bool cplx) {
+                                bool cplx, unsigned max_ctas) {
   if (nblocks_x == 0 || nblocks_y == 0)
     return cudaSuccess;
 #define DLAFB_SHAPE(BM, BN, ST, MB)                                                                  \
-  return cplx ? launch_shape<BM, BN, ST, MB, true>(stream, map_a, map_b, p, nblocks_x, nblocks_y)    \
-              : launch_shape<BM, BN, ST, MB, false>(stream, map_a, map_b, p, nblocks_x, nblocks_y)
+  return cplx ? launch_shape<BM, BN, ST, MB, true>(stream, map_a, map_b, p, nblocks_x, nblocks_y, max_ctas)    \
+              : launch_shape<BM, BN, ST, MB, false>(stream, map_a, map_b, p, nblocks_x, nblocks_y, max_ctas)
   switch (shape) {
     case GemmShape::k128x128:
       DLAFB_SHAPE(128, 128, 4, 1);

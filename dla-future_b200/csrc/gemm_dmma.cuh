@@ -76,6 +76,10 @@ int make_operand_map(CUtensorMap* map, const double* base, long long rows, long 
 // Launches the kernel for `nblocks_x` x `nblocks_y` CTAs on `stream`. The maps' boxes must match `shape`.
 cudaError_t launch_gemm_nt_dmma(cudaStream_t stream, const CUtensorMap& map_a, const CUtensorMap& map_b,
                                 const GemmParams& p, unsigned nblocks_x, unsigned nblocks_y,
-                                GemmShape shape = GemmShape::k128x128, bool cplx = false);
+                                GemmShape shape = GemmShape::k128x128, bool cplx = false, unsigned max_ctas = 0);
+// max_ctas > 0: at most that many CTAs, each looping over blocks b, b + grid, ... (persistent). The engine uses it
+// with one CTA per SM minus one SM when the dependent chain of the factorization is the bottleneck: the
+// high-priority kernels then always find a free half SM (and the single-CTA diagonal kernel a whole one).
+int gemm_sm_count();
 
 }  // namespace dlafb

@@ -71,6 +71,17 @@ StreamWaitValue32Fn stream_wait_value32() {
   return fn;
 }
 
+// bulk launches with fewer 128 x 128 blocks than this leave SM slots to the high-priority stream (see update()).
+// Experiment, off by default: one persistent CTA per SM runs the update at ~55 % of the two-CTA rate and the
+// look-ahead update then only gets the other half slots: n=16384 on 1 GPU 49.1 -> 51.7 ms with 3000.
+size_t reserve_below() {
+  static const size_t v = [] {
+    const char* e = getenv("DLAFB_RESERVE_BELOW");
+    return e ? (size_t)atoll(e) : (size_t)0;  // off: measured slower (profiles/r01/reserve_sweep.txt)
+  }();
+  return v;
+}
+
 // shape of the bulk launches (DLAFB_BULK_SHAPE=0: one 128 x 128 CTA per SM, 3: two 64 x 128 CTAs per SM)
 GemmShape bulk_shape() {
   static const GemmShape s = [] {
@@ -544,7 +555,7 @@ struct Plan final : dlafb_chol_plan {
   // serial chain of nb/16 slices, so 4x more, 4x shorter CTAs end the launch sooner (the look-ahead column and the
   // last steps are on the critical path).
   int update(cudaStream_t s, T* A, int64_t ld, const CUtensorMap* map_a_local, int nbox_local, int64_t k, int buf,
-             size_t off, size_t count) {
+             size_t off, size_t count, bool bulk = false) {
     if (count == 0)
       return 0;
     if (fast) {
@@ -563,15 +574,19 @@ struct Plan final : dlafb_chol_plan {
       const GemmShape shape = big < kSmallShapeBelow ? GemmShape::k64x64 : bulk_shape();
       const int bm = shape_bm(shape), bn = shape_bn(shape);
       const unsigned ctas = (unsigned)(count * (p.tile / bm) * (p.tile / bn));
+      // Bulk launch short enough that the dependent chain (diagonal tile -> panel solve -> exchange) decides the
+      // step time: run it as one persistent CTA per SM on all SMs but one. Every high-priority kernel then finds a
+      // free half SM at once, the single-CTA diagonal kernel a whole SM, instead of waiting for update CTAs to retire.
+      const unsigned cap = (bulk && big < reserve_below()) ? (unsigned)std::max(1, gemm_sm_count() - 1) : 0u;
       if (dist) {
         p.nbox_a = p.nbox_b = 4;
         return (int)launch_gemm_nt_dmma(s, bm == 64 ? map_pr_s[buf] : map_pr[buf], bn == 64 ? map_pc_s[buf] : map_pc[buf],
-                                        p, ctas, 1, shape, cplx);
+                                        p, ctas, 1, shape, cplx, cap);
       }
       p.a_col0 = p.b_col0 = (int)(k * nb);
       p.nbox_a = p.nbox_b = nbox_local;
       return (int)launch_gemm_nt_dmma(s, map_a_local[bm == 64 ? 1 : 0], map_a_local[bn == 64 ? 1 : 0], p, ctas, 1, shape,
-                                      cplx);
+                                      cplx, cap);
     }
     SimtParams<T> p{};
     p.C = A;
@@ -901,7 +916,7 @@ struct Plan final : dlafb_chol_plan {
         const bool timed = profiling && np_cnt > 0;
         if (timed)
           CU(cudaEventRecord(pev[2 * k], np));
-        r = update(np, A, ld, map_local, nbox_local, k, buf, np_off[k], np_cnt);
+        r = update(np, A, ld, map_local, nbox_local, k, buf, np_off[k], np_cnt, true);
         if (r != 0)
           return r;
         if (timed)
