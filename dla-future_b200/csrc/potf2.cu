@@ -1,21 +1,22 @@
 // Diagonal-block Cholesky: a latency-bound single-CTA kernel that keeps the whole block in shared memory.
 // Replaces cusolverDn{S,D,C,Z}potrf on the diagonal tile (reference: include/dlaf/lapack/tile.h:578-606,
-// called from include/dlaf/factorization/cholesky/impl.h:46-53 and :98-105).
+// called from include/dlaf/factorization/cholesky/impl.h:46-53 and :98-105) and also forms W = inv(L): the panel
+// solve multiplies by W^H with the DMMA contraction kernel instead of substituting.
 //
-// One CTA of 512 threads, block order n <= Potf2Limits<T>::nmax, inner step BS (32, or 16 for complex<double>):
-//   panel: every row of the BS-wide column panel (diagonal sub-block AND the rows below it) lives in the registers
-//          of one thread; per column the pivot column of the sub-block is published through a double-buffered
-//          shared array, ONE block barrier per column, 1/sqrt by rsqrt (no divide on the dependent chain);
-//   update: trailing lower triangle with register-tiled accumulators, all 512 threads.
-// The same CTA then forms W = inv(L) (the panel solve multiplies by W^H with the DMMA contraction kernel instead of
-// substituting): the BS x BS diagonal blocks by forward substitution (one column per thread, in registers), the
-// off-diagonal blocks by block distance, W_ij = -W_ii * (sum_l L_il W_lj), with 2 x 2 register tiles; W^T is kept in
-// the strict upper triangle of the shared buffer.
+// One CTA of 512 threads, block order n <= Potf2Limits<T>::nmax (128; 64 for complex<double>), panels of 8 columns:
+//   panel:  one thread per row keeps its row of the panel in registers; threads [NMAX, 2*NMAX) own the rows of an
+//           identity appended below A, which the same column operations turn into inv(L)^H, so the inverse adds no
+//           dependent chain of its own. Every participating warp factors the 8 x 8 diagonal sub-block itself
+//           (lane l keeps row l % 8, columns travel by warp shuffle, the diagonal is tracked by every lane), so the
+//           column-to-column chain is rsqrt -> scale -> FMA: no block barrier, no shared-memory round trip;
+//   update: trailing columns (A rows below and E rows above) with 4 x CBN register tiles, all 512 threads,
+//           instantiated per column count; loads and stores are select/predicate only.
 // `info` follows potrf: index (1-based, offset by info_base) of the first non-positive pivot, first failure wins.
 //
-// History (round 1): the first version factored the sub-block in ONE warp with warp-shuffle broadcasts and solved
-// the rows below with one thread per row; measured 143 us (factor) + 116 us (inverse) for n = 128
-// (profiles/r01/critical_path_v1.json), i.e. 1.17 ms per 512 tile on the critical path. This version replaces both.
+// History (round 1, profiles/r01/critical_path_v*.json): v1 factored the sub-block in ONE warp and solved the rows
+// below with one thread per row, then inverted separately: 252 us for n = 128. A 32-column, fully unrolled register
+// variant: 131 us (FP64 dependent latency is 23 cycles on B200, issue 2.2 cycles per warp instruction:
+// profiles/r01/latency_b200.txt). This version: 75 us; the 512 x 512 tile built from it: 1170 -> 362 us.
 #include "tile_ops.cuh"
 
 namespace dlafb {
@@ -60,9 +61,6 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
     for (int ia = 0; ia < RA; ++ia)
       acc[ia][ib] = Tr<T>::zero();
   }
-#ifdef DLAFB_EXP_NOLOOP
-  if (bs > 100)
-#endif
 #pragma unroll 2
   for (int l = 0; l < bs; ++l) {
     const T* xp = Xp + l * NMAX;
@@ -88,9 +86,6 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
     for (int ia = 0; ia < RA; ++ia) {
       const int rw = tx + 32 * ia;
       const bool keep = colok && rw < n && ((factor && rw >= col) || (inv && rw < r0));
-#ifdef DLAFB_EXP_NORMW
-      if (bs > 100)
-#endif
       dcol[rw] = Tr<T>::add(dcol[rw], keep ? acc[ia][ib] : Tr<T>::zero());
     }
   }
