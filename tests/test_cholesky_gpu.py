@@ -103,3 +103,58 @@ def test_repeated_runs_same_plan(pkg, L):
     assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[1], outs[2])   # deterministic
     plan.close()
     grid.close()
+
+
+def test_profiling_timeline_and_exchange_mode(pkg, L):
+    """The profiling hooks bench.py relies on: per-step marks are monotonic on each stream and the bulk-update
+    timing adds up; a single-rank plan reports the 'local' exchange mode."""
+    n, nb = 2048, 256
+    a = orc.gen_hpd(n, nb, np.float64)
+    grid = pkg.Grid(L)
+    plan = pkg.CholeskyPlan(L, grid, "d", "L", n, nb)
+    assert plan.exchange_mode() == "local"
+    plan.set_profiling(True)
+    A = DevMat(a, ld=n)
+    plan.run(A.ptr, A.ld, stream_ptr())
+    assert plan.info() == 0
+    ms, flops, launches = plan.profile()
+    tl = plan.timeline()
+    nt = n // nb
+    assert len(tl) == nt and launches == nt - 2 and ms > 0 and flops > 0
+    for k in range(nt - 1):
+        hp = tl[k][:6]
+        assert all(x >= 0 for x in hp) and all(hp[i] <= hp[i + 1] + 1e-3 for i in range(5))
+        if k < nt - 2:
+            assert 0 <= tl[k][6] <= tl[k][7]
+    assert all(x == -1.0 for x in tl[nt - 1])
+    plan.set_profiling(False)
+    want = a.copy(order="F")
+    assert orc.cholesky_local("L", want, nb) == 0
+    assert np.abs(np.tril(A.get()) - np.tril(want)).max() < 1e-10
+    plan.close()
+    grid.close()
+
+
+@pytest.mark.parametrize("uplo", "LU")
+def test_run_host_moves_only_the_referenced_triangle(pkg, L, uplo):
+    """dlafb_cholesky_plan_run_host: device mirror supplied by the caller, pinned or pageable host block; the
+    unreferenced triangle of the host block stays untouched and the mirror's one is never read."""
+    import ctypes
+    import torch
+    n, nb = 1536, 256
+    a = orc.gen_hpd(n, nb, np.float64)
+    want = a.copy(order="F")
+    assert orc.cholesky_local(uplo, want, nb) == 0
+    ref = np.tril(np.ones((n, n), bool)) if uplo == "L" else np.triu(np.ones((n, n), bool))
+    host = np.where(ref, a, -9.9).T.copy()           # column-major n x n, ld = n
+    dev = torch.full((n * n + 64,), float("nan"), dtype=torch.float64, device="cuda")   # poisoned mirror
+    grid = pkg.Grid(L)
+    plan = pkg.CholeskyPlan(L, grid, "d", uplo, n, nb)
+    pkg.check(L.dlafb_cholesky_plan_run_host(plan.h, host.ctypes.data, n, dev.data_ptr(), n, stream_ptr()), "run_host")
+    assert plan.info() == 0
+    sync()
+    got = host.T
+    assert np.abs(np.where(ref, got - want, 0)).max() < 1e-10
+    assert np.all(got[~ref] == -9.9)
+    plan.close()
+    grid.close()
