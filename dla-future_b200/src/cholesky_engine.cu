@@ -163,6 +163,17 @@ struct Plan final : dlafb_chol_plan {
   cudaEvent_t ev_col = nullptr, ev_dh_end = nullptr;
   T* sink = nullptr;
   int64_t sink_ld = 0;
+  // ... and (single rank) the host block ARRIVES in kUpGroups groups of tile columns of about equal bytes on `uh`
+  // while the first steps already run: during the first `up_steps` steps the bulk update is one launch per group on
+  // the group's own stream, which waits for that group's upload only.
+  static constexpr int kUpGroups = 8;
+  cudaStream_t uh = nullptr, gs[kUpGroups] = {};
+  cudaEvent_t ev_up[kUpGroups] = {}, ev_grp[kUpGroups] = {};
+  std::vector<int> grp_of_col;                 // local tile column -> upload group
+  std::vector<size_t> split_off;               // [step * (kUpGroups + 1) + g]: range in lists_split
+  int2* lists_split = nullptr;
+  int64_t up_steps = 0;                        // steps with a split bulk update (0: no overlap possible)
+  bool up_on = false;                          // this run uploads while it computes
   cudaEvent_t ev_in = nullptr, ev_panel[2] = {nullptr, nullptr}, ev_np[2] = {nullptr, nullptr}, ev_hp_end = nullptr,
               ev_np_end = nullptr;
   T* D = nullptr;  // [inverted diagonal blocks (nblk*ib*ib) | diagonal tile (nb*nb, ld = nb)]
@@ -217,6 +228,13 @@ struct Plan final : dlafb_chol_plan {
     if (ev_ladiag) cudaEventDestroy(ev_ladiag);
     if (ev_potrf) cudaEventDestroy(ev_potrf);
     if (dh) cudaStreamDestroy(dh);
+    if (uh) cudaStreamDestroy(uh);
+    for (int g = 0; g < kUpGroups; ++g) {
+      if (gs[g]) cudaStreamDestroy(gs[g]);
+      if (ev_up[g]) cudaEventDestroy(ev_up[g]);
+      if (ev_grp[g]) cudaEventDestroy(ev_grp[g]);
+    }
+    cudaFree(lists_split);
     if (ev_col) cudaEventDestroy(ev_col);
     if (ev_dh_end) cudaEventDestroy(ev_dh_end);
     for (cudaEvent_t e : {ev_in, ev_panel[0], ev_panel[1], ev_np[0], ev_np[1], ev_hp_end, ev_np_end})
@@ -539,6 +557,39 @@ struct Plan final : dlafb_chol_plan {
       CU(cudaMalloc(&lists, all.size() * sizeof(int2)));
       CU(cudaMemcpy(lists, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
     }
+    if (!dist && !upper && nt >= 16) {
+      // upload groups of about equal bytes (the first tile columns are the longest)
+      grp_of_col.assign((size_t)nt, 0);
+      double total = 0, acc = 0;
+      for (int64_t j = 0; j < nt; ++j)
+        total += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
+      for (int64_t j = 0; j < nt; ++j) {
+        grp_of_col[(size_t)j] = std::min<int>(kUpGroups - 1, (int)(acc * kUpGroups / total));
+        acc += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
+      }
+      const char* ue = getenv("DLAFB_UP_STEPS");
+      up_steps = std::min<int64_t>(ue ? atoll(ue) : 10, nt - 2);
+      std::vector<int2> sp;
+      split_off.assign((size_t)up_steps * (kUpGroups + 1), 0);
+      for (int64_t k = 0; k < up_steps; ++k)
+        for (int g = 0; g <= kUpGroups; ++g) {
+          split_off[(size_t)k * (kUpGroups + 1) + g] = sp.size();
+          if (g < kUpGroups)
+            for (const UpdateTile& t : sched.steps[k].np)
+              if (grp_of_col[(size_t)(t.col / nb)] == g)
+                sp.push_back(make_int2(t.row, t.col | (t.diag ? (int)0x80000000 : 0)));
+        }
+      if (!sp.empty()) {
+        CU(cudaMalloc(&lists_split, sp.size() * sizeof(int2)));
+        CU(cudaMemcpy(lists_split, sp.data(), sp.size() * sizeof(int2), cudaMemcpyHostToDevice));
+      }
+      CU(cudaStreamCreateWithFlags(&uh, cudaStreamNonBlocking));
+      for (int g = 0; g < kUpGroups; ++g) {
+        CU(cudaStreamCreateWithPriority(&gs[g], cudaStreamNonBlocking, lo));
+        CU(cudaEventCreateWithFlags(&ev_up[g], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ev_grp[g], cudaEventDisableTiming));
+      }
+    }
     np_flops.assign(nt + 1, 0.0);
     for (int64_t k = 0; k < nt; ++k)
       for (const UpdateTile& t : sched.steps[k].np)
@@ -555,7 +606,9 @@ struct Plan final : dlafb_chol_plan {
   // serial chain of nb/16 slices, so 4x more, 4x shorter CTAs end the launch sooner (the look-ahead column and the
   // last steps are on the critical path).
   int update(cudaStream_t s, T* A, int64_t ld, const CUtensorMap* map_a_local, int nbox_local, int64_t k, int buf,
-             size_t off, size_t count, bool bulk = false) {
+             size_t off, size_t count, bool bulk = false, const int2* list_base = nullptr) {
+    if (!list_base)
+      list_base = lists;
     if (count == 0)
       return 0;
     if (fast) {
@@ -567,7 +620,7 @@ struct Plan final : dlafb_chol_plan {
       p.K = (int)nb;
       p.alpha = -1.0;
       p.beta = 1.0;
-      p.list = lists + off;
+      p.list = list_base + off;
       p.tile = (int)(nb * vs);
       p.list_scale = vs;
       const size_t big = count * (p.tile / 128) * (p.tile / 128);
@@ -596,7 +649,7 @@ struct Plan final : dlafb_chol_plan {
     p.K = (int)nb;
     p.alpha = R(-1);
     p.beta = R(1);
-    p.list = lists + off;
+    p.list = list_base + off;
     p.sub = (int)((nb + kSimtTile - 1) / kSimtTile);
     p.tile = (int)nb;
     if (dist) {
@@ -661,21 +714,40 @@ struct Plan final : dlafb_chol_plan {
     T* dev = static_cast<T*>(dev_);
     if (n <= 0)
       return run(dev, ldd, user);
+    const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(dev) & 15) || ((ldd * vs) & 1));
+    const bool overlap = !upper && !misaligned;  // the other cases factor a transposed / realigned copy
+    // single rank: the upload runs on its own stream, group after group, and the factorization starts with the
+    // first group; otherwise the whole triangle is uploaded first
+    const bool stream_in = overlap && up_steps > 0 && uh != nullptr;
+    cudaStream_t us = stream_in ? uh : user;
+    if (stream_in) {
+      CU(cudaEventRecord(ev_in, user));
+      CU(cudaStreamWaitEvent(uh, ev_in, 0));
+    }
+    int last_g = 0;
     int e = for_each_triangle_block([&](int64_t r0, int64_t nr, int64_t c0, int64_t nc) {
+      if (stream_in) {
+        const int g = grp_of_col[(size_t)(c0 / nb)];
+        for (; last_g < g; ++last_g)
+          CU(cudaEventRecord(ev_up[last_g], uh));
+      }
       CU(cudaMemcpy2DAsync(dev + r0 + (size_t)c0 * ldd, (size_t)ldd * sizeof(T), host + r0 + (size_t)c0 * ldh,
-                           (size_t)ldh * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc, cudaMemcpyHostToDevice, user));
+                           (size_t)ldh * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc, cudaMemcpyHostToDevice, us));
       return 0;
     });
     if (e != 0)
       return e;
-    const bool misaligned = fast && ((reinterpret_cast<uintptr_t>(dev) & 15) || ((ldd * vs) & 1));
-    const bool overlap = !upper && !misaligned;  // the other cases factor a transposed / realigned copy
+    if (stream_in)
+      for (; last_g < kUpGroups; ++last_g)
+        CU(cudaEventRecord(ev_up[last_g], uh));
+    up_on = stream_in;
     if (overlap) {
       sink = host;
       sink_ld = ldh;
     }
     e = run(dev, ldd, user);
     sink = nullptr;
+    up_on = false;
     if (e != 0)
       return e;
     if (overlap) {
@@ -721,7 +793,7 @@ struct Plan final : dlafb_chol_plan {
       T* DW = Dk[buf];
       T* DL = DW + (size_t)nblk * ib * ib;
       // global step number: the counters in the peers' arenas never restart (pp.epoch = runs so far)
-      const uint32_t gs = (uint32_t)(pp.epoch * (uint64_t)nt + (uint64_t)k);
+      const uint32_t gstep = (uint32_t)(pp.epoch * (uint64_t)nt + (uint64_t)k);
       if (pp.on) {
         // my copies of step k-2 out of Pr[buf] / Dk[buf] must have left before this step overwrites them
         for (int q = 0; q < Q; ++q)
@@ -737,6 +809,12 @@ struct Plan final : dlafb_chol_plan {
       const bool mark = profiling && !last;
       if (mark)
         CU(cudaEventRecord(hev[6 * k + 0], hp));
+      if (up_on) {
+        // tile column k (and k+1 for the look-ahead update) must have arrived from the host
+        CU(cudaStreamWaitEvent(hp, ev_up[grp_of_col[(size_t)k]], 0));
+        if (!last)
+          CU(cudaStreamWaitEvent(hp, ev_up[grp_of_col[(size_t)(k + 1)]], 0));
+      }
       if (st.own_diag) {
         Akk = A + (size_t)st.lk_row * nb + (size_t)st.lk_col * nb * ld;
         if (diag_ahead) {
@@ -782,16 +860,16 @@ struct Plan final : dlafb_chol_plan {
                   continue;
                 cudaStream_t cs = pp.cs_col[(size_t)r];
                 CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
-                if (gs >= 2)
-                  PP(wait_flag(cs, f_done_col(r), gs - 1));
+                if (gstep >= 2)
+                  PP(wait_flag(cs, f_done_col(r), gstep - 1));
                 CU(cudaMemcpyAsync(pp.col_peer[(size_t)r] + pp.off_D[buf], DW, d_elems * sizeof(T),
                                    cudaMemcpyDeviceToDevice, cs));
-                PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_d(buf), gs + 1));
+                PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_d(buf), gstep + 1));
                 CU(cudaEventRecord(pp.ev_col_sent[buf][(size_t)r], cs));
               }
             }
             else if (P > 1) {
-              PP(wait_flag(hp, f_sig_d(buf), gs + 1));
+              PP(wait_flag(hp, f_sig_d(buf), gstep + 1));
             }
             const T* Lkk = (P > 1) ? DL : Akk;
             const int64_t ldl = (P > 1) ? nb : ld;
@@ -820,16 +898,16 @@ struct Plan final : dlafb_chol_plan {
                 continue;
               cudaStream_t cs = pp.cs_row[(size_t)q];
               CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
-              if (gs >= 2)
-                PP(wait_flag(cs, f_done_row(q), gs - 1));
+              if (gstep >= 2)
+                PP(wait_flag(cs, f_done_row(q), gstep - 1));
               CU(cudaMemcpyAsync(pp.row_peer[(size_t)q] + pp.off_Pr[buf] + o, reinterpret_cast<uint8_t*>(Pr[buf]) + o,
                                  row_cnt * sizeof(T), cudaMemcpyDeviceToDevice, cs));
-              PP(raise_flag(cs, pp.row_peer[(size_t)q], f_sig_row(buf), gs + 1));
+              PP(raise_flag(cs, pp.row_peer[(size_t)q], f_sig_row(buf), gstep + 1));
               CU(cudaEventRecord(pp.ev_row_sent[buf][(size_t)q], cs));
             }
           }
           else if (Q > 1 && row_cnt > 0) {
-            PP(wait_flag(hp, f_sig_row(buf), gs + 1));
+            PP(wait_flag(hp, f_sig_row(buf), gstep + 1));
           }
           if (mark)
             CU(cudaEventRecord(hev[6 * k + 3], hp));
@@ -853,19 +931,19 @@ struct Plan final : dlafb_chol_plan {
                     continue;
                   cudaStream_t cs = pp.cs_col[(size_t)r];
                   CU(cudaStreamWaitEvent(cs, pp.ev_src, 0));
-                  if (gs >= 2)
-                    PP(wait_flag(cs, f_done_col(r), gs - 1));
+                  if (gstep >= 2)
+                    PP(wait_flag(cs, f_done_col(r), gstep - 1));
                   for (const ColBcast& cb : st.colb)
                     if (cb.root == pr)
                       CU(cudaMemcpyAsync(pp.col_peer[(size_t)r] + pp.off_Pc[buf] + (size_t)cb.jl * slotb,
                                          Pr[buf] + (size_t)cb.src_il * slot, slotb, cudaMemcpyDeviceToDevice, cs));
-                  PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_col(buf, pr), gs + 1));
+                  PP(raise_flag(cs, pp.col_peer[(size_t)r], f_sig_col(buf, pr), gstep + 1));
                   CU(cudaEventRecord(pp.ev_col_sent[buf][(size_t)r], cs));
                 }
               }
               for (int r = 0; r < P; ++r)
                 if (r != pr && from[(size_t)r])
-                  PP(wait_flag(hp, f_sig_col(buf, r), gs + 1));
+                  PP(wait_flag(hp, f_sig_col(buf, r), gstep + 1));
             }
             else if (P > 1) {
               NC(ncclGroupStart());
@@ -892,7 +970,9 @@ struct Plan final : dlafb_chol_plan {
         }
         CU(cudaEventRecord(ev_panel[buf], hp));
         // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
-        if (k >= 1)
+        if (k >= 1 && up_on && k - 1 < up_steps)
+          CU(cudaStreamWaitEvent(hp, ev_grp[grp_of_col[(size_t)(k + 1)]], 0));  // split bulk update of step k-1
+        else if (k >= 1)
           CU(cudaStreamWaitEvent(hp, ev_np[(k - 1) & 1], 0));
         int r = 0;
         size_t la_off = hp_off[k], la_cnt = np_off[k] - hp_off[k];
@@ -911,6 +991,30 @@ struct Plan final : dlafb_chol_plan {
           return r;
         if (mark)
           CU(cudaEventRecord(hev[6 * k + 5], hp));
+        if (up_on && k < up_steps) {
+          // one launch per upload group on the group's stream: the groups that have arrived run ahead
+          for (int g = 0; g < kUpGroups; ++g) {
+            const size_t o = split_off[(size_t)k * (kUpGroups + 1) + g];
+            const size_t c = split_off[(size_t)k * (kUpGroups + 1) + g + 1] - o;
+            if (c == 0)
+              continue;
+            if (k == 0)
+              CU(cudaStreamWaitEvent(gs[g], ev_in, 0));
+            CU(cudaStreamWaitEvent(gs[g], ev_up[g], 0));
+            CU(cudaStreamWaitEvent(gs[g], ev_panel[buf], 0));
+            r = update(gs[g], A, ld, map_local, nbox_local, k, buf, o, c, true, lists_split);
+            if (r != 0)
+              return r;
+            CU(cudaEventRecord(ev_grp[g], gs[g]));
+          }
+          np_timed[k] = 0;
+          continue;
+        }
+        if (up_on && k == up_steps)
+          for (int g = 0; g < kUpGroups; ++g) {  // join: from here on one launch per step again
+            CU(cudaStreamWaitEvent(np, ev_grp[g], 0));
+            CU(cudaStreamWaitEvent(np, ev_up[g], 0));
+          }
         CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
         const size_t np_cnt = (k + 1 < nt ? hp_off[k + 1] : np_off[k]) - np_off[k];
         const bool timed = profiling && np_cnt > 0;
@@ -936,10 +1040,10 @@ struct Plan final : dlafb_chol_plan {
             CU(cudaStreamWaitEvent(np, pp.ev_col_sent[buf][(size_t)r], 0));
         for (int q = 0; q < Q; ++q)
           if (q != pc)
-            PP(raise_flag(np, pp.row_peer[(size_t)q], f_done_row(pc), gs + 1));
+            PP(raise_flag(np, pp.row_peer[(size_t)q], f_done_row(pc), gstep + 1));
         for (int r = 0; r < P; ++r)
           if (r != pr)
-            PP(raise_flag(np, pp.col_peer[(size_t)r], f_done_col(pr), gs + 1));
+            PP(raise_flag(np, pp.col_peer[(size_t)r], f_done_col(pr), gstep + 1));
       }
     }
     if (pp.on) {

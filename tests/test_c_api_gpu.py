@@ -41,7 +41,8 @@ def referenced(n, uplo):
 
 @pytest.mark.parametrize("x", "sdcz")
 @pytest.mark.parametrize("uplo", "LU")
-@pytest.mark.parametrize("n,nb,extra", [(34, 13, 0), (300, 128, 5), (1000, 128, 24), (1024, 256, 0), (1536, 512, 0)])
+@pytest.mark.parametrize("n,nb,extra", [(34, 13, 0), (300, 128, 5), (1000, 128, 24), (1024, 256, 0), (1536, 512, 0),
+                                          (2304, 128, 8)])   # >= 16 tile columns: upload overlapped with the first steps
 def test_pxpotrf_host_pointer(pkg, capi, x, uplo, n, nb, extra):
     L = capi
     dt = NP[x]

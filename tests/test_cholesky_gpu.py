@@ -135,13 +135,12 @@ def test_profiling_timeline_and_exchange_mode(pkg, L):
     grid.close()
 
 
+@pytest.mark.parametrize("n,nb", [(1536, 256), (4096, 256), (2560, 128)])
 @pytest.mark.parametrize("uplo", "LU")
-def test_run_host_moves_only_the_referenced_triangle(pkg, L, uplo):
+def test_run_host_moves_only_the_referenced_triangle(pkg, L, uplo, n, nb):
     """dlafb_cholesky_plan_run_host: device mirror supplied by the caller, pinned or pageable host block; the
     unreferenced triangle of the host block stays untouched and the mirror's one is never read."""
-    import ctypes
     import torch
-    n, nb = 1536, 256
     a = orc.gen_hpd(n, nb, np.float64)
     want = a.copy(order="F")
     assert orc.cholesky_local(uplo, want, nb) == 0
@@ -156,5 +155,11 @@ def test_run_host_moves_only_the_referenced_triangle(pkg, L, uplo):
     got = host.T
     assert np.abs(np.where(ref, got - want, 0)).max() < 1e-10
     assert np.all(got[~ref] == -9.9)
+    # same plan again (the upload-group events and streams are reused), pinned host block this time
+    pinned = torch.from_numpy(np.where(ref, a, -9.9).T.copy()).pin_memory()
+    pkg.check(L.dlafb_cholesky_plan_run_host(plan.h, pinned.data_ptr(), n, dev.data_ptr(), n, stream_ptr()), "run_host")
+    assert plan.info() == 0
+    sync()
+    assert np.array_equal(pinned.numpy().T, got)
     plan.close()
     grid.close()
