@@ -20,6 +20,8 @@ import sys
 import threading
 import time
 
+# read at CUDA context creation: the engine uses more streams than the default 8 hardware queues (see grid.cu)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 FP64_PEAK_FILE = os.path.join(ROOT, "profiles", "fp64_peak_r01.json")
 

@@ -20,6 +20,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cmath>
 #include <type_traits>
 #include <cstdlib>
 #include <vector>
@@ -163,7 +164,7 @@ struct Plan final : dlafb_chol_plan {
   cudaEvent_t ev_col = nullptr, ev_dh_end = nullptr;
   T* sink = nullptr;
   int64_t sink_ld = 0;
-  // ... and (single rank) the host block ARRIVES in kUpGroups groups of tile columns of about equal bytes on `uh`
+  // ... and (single rank) the host block ARRIVES in kUpGroups groups of tile columns (growing in size) on `uh`
   // while the first steps already run: during the first `up_steps` steps the bulk update is one launch per group on
   // the group's own stream, which waits for that group's upload only.
   static constexpr int kUpGroups = 8;
@@ -558,13 +559,14 @@ struct Plan final : dlafb_chol_plan {
       CU(cudaMemcpy(lists, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
     }
     if (!dist && !upper && nt >= 16) {
-      // upload groups of about equal bytes (the first tile columns are the longest)
+      // upload groups of growing size
       grp_of_col.assign((size_t)nt, 0);
       double total = 0, acc = 0;
       for (int64_t j = 0; j < nt; ++j)
         total += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
       for (int64_t j = 0; j < nt; ++j) {
-        grp_of_col[(size_t)j] = std::min<int>(kUpGroups - 1, (int)(acc * kUpGroups / total));
+        // group g ends at the fraction ((g+1)/G)^2 of the bytes: small first groups start the factorization early
+        grp_of_col[(size_t)j] = std::min<int>(kUpGroups - 1, (int)(std::sqrt(acc / total) * kUpGroups));
         acc += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
       }
       const char* ue = getenv("DLAFB_UP_STEPS");

@@ -1,4 +1,5 @@
 // Process grid over NCCL, index-algebra and schedule exports (see include/dlafb_engine.h).
+#include <cstdlib>
 #include "grid.h"
 
 #include <cstring>
@@ -213,3 +214,14 @@ int dlafb_schedule_step(int64_t n, int64_t nb, int P, int Q, int pr, int pc, int
 uint64_t dlafb_launch_count(void) { return g_launches.load(); }
 
 }  // extern "C"
+
+// The engine drives up to 14 streams per rank (two priority streams, bulk, diagonal, copy-in groups, copy-out, peer
+// copies). With the default of 8 hardware work queues several of them alias and serialise (measured: the
+// host-mirrored run 394 ms instead of 365 ms at n = 32768, profiles/r01/e2e_probe.txt). The variable is read when the
+// CUDA context is created, so it is set when the library is loaded, unless the user already chose a value.
+namespace {
+__attribute__((constructor)) void dlafb_more_hw_queues() {
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+}
+}  // namespace
+
