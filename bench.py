@@ -252,8 +252,27 @@ def main():
     ms = sum(times) / len(times)
     gflops = flops_cholesky(n) / (ms * 1e-3) / 1e9
 
-    # ---- residual of the last factorization (miniapp check, 1 GPU only: needs the whole matrix in one place) ----
+    # ---- residual of the last factorization on the device, distributed like the matrix (any number of ranks):
+    #      max|A - L L^T| / max|A| <= n*eps, miniapp_cholesky.cpp:408-442 ----
     check = None
+    engine_check = None
+    if not args.no_check:
+        try:
+            a0buf = torch.empty_like(a)
+            pkg.check(L.dlafb_gen_hpd_d(stream, n, nb, rows, cols, row_first, P, col_first, Q, a0buf.data_ptr(), ld,
+                                        100 + args.steps - 1), "gen")
+            amax_g, dmax_g = plan.residual(a0buf.data_ptr(), ld, a.data_ptr(), ld, stream)
+            eps = 2.220446049250313e-16
+            engine_check = {"max_norm_ratio": dmax_g / amax_g, "threshold_n_eps": n * eps,
+                            "pass": bool(dmax_g / amax_g <= n * eps), "info": info,
+                            "by": "dlafb_cholesky_plan_residual (distributed, on the device)"}
+            del a0buf
+        except Exception as ex:
+            engine_check = {"error": str(ex)[:200]}
+        if world > 1:
+            check = engine_check
+
+    # ---- the same residual with torch.matmul as an independent checker (1 GPU: whole matrix in one place) ----
     if world == 1 and not args.no_check:
         try:
             l_ = torch.as_strided(a, (n, n), (1, ld)).tril()
@@ -333,6 +352,7 @@ def main():
                                  "dram bytes read+written by the step-0 bulk launch of the n=32768 workload "
                                  "(profiles/r01/ncu_update_kernel.json: 94.5 % tensor pipe for the kernel alone)"},
             "clocks": clocks, "gpu_launches": int(launches), "exchange": exchange, "e2e": e2e, "check": check,
+            "engine_check": engine_check,
             "times_ms": [round(t, 2) for t in times],
         }
         if not args.no_cpu and world == 1:

@@ -44,6 +44,7 @@ ENGINE_API = {
     "dlafb_cholesky_plan_profile": (c_int, [c_vp, P_dbl, P_dbl, P_int]),
     "dlafb_cholesky_plan_timeline": (c_int, [c_vp, P_dbl, ctypes.c_longlong]),
     "dlafb_cholesky_plan_exchange_mode": (c_int, [c_vp]),
+    "dlafb_cholesky_plan_residual": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, P_dbl, P_dbl]),
     "dlafb_launch_count": (ctypes.c_uint64, []),
 }
 
@@ -133,6 +134,13 @@ class CholeskyPlan:
         ms, fl, n = ctypes.c_double(), ctypes.c_double(), c_int()
         _ck(self.L.dlafb_cholesky_plan_profile(self.h, ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(n)), "profile")
         return ms.value, fl.value, n.value
+
+    def residual(self, a0_ptr, lda, l_ptr, ldl, stream):
+        """(max|A0|, max|A0 - L L^H|) over the grid; a0 is overwritten. Collective."""
+        a, d = ctypes.c_double(), ctypes.c_double()
+        _ck(self.L.dlafb_cholesky_plan_residual(self.h, a0_ptr, lda, l_ptr, ldl, stream, ctypes.byref(a),
+                                                ctypes.byref(d)), "residual")
+        return a.value, d.value
 
     def exchange_mode(self):
         return {0: "local", 1: "nccl", 2: "p2p"}.get(self.L.dlafb_cholesky_plan_exchange_mode(self.h), "?")

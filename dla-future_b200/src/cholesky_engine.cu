@@ -43,6 +43,7 @@ struct dlafb_chol_plan {
   virtual int profile(double* ms, double* flops, int* launches) = 0;
   virtual int timeline(double* out, long long cap) = 0;
   virtual int exchange_mode() const = 0;
+  virtual int residual(void* a0, int64_t lda, const void* l, int64_t ldl, cudaStream_t stream, double* out2) = 0;
   bool profiling = false;
 };
 
@@ -142,9 +143,16 @@ struct Plan final : dlafb_chol_plan {
 
   // configuration (L orientation: for uplo = 'U' rows and columns of the grid are swapped)
   bool upper = false;
+  int src_r = 0, src_c = 0;
   int64_t n = 0, nb = 1;
   int P = 1, Q = 1, pr = 0, pc = 0;
-  ncclComm_t rowc = nullptr, colc = nullptr;
+  ncclComm_t rowc = nullptr, colc = nullptr, worldc = nullptr;
+  // residual checker (lazy): inclusive schedule, its lists, panel buffers of a single-rank plan, results
+  Schedule rsched;
+  int2* rlists = nullptr;
+  std::vector<size_t> r_off;
+  double* r_out = nullptr;
+  bool r_ready = false;
   Schedule sched;
   int64_t nt = 0, mloc = 0, nloc = 0;  // local rows / cols (L orientation)
   bool dist = false;                   // more than one rank
@@ -260,10 +268,13 @@ struct Plan final : dlafb_chol_plan {
     if (!pp.base)
       for (int b = 0; b < 2; ++b) {
         cudaFree(Pr[b]);
-        cudaFree(Pc[b]);
+        if (Pc[b] != Pr[b])  // the residual checker of a single-rank plan aliases them
+          cudaFree(Pc[b]);
       }
     cudaFree(pp.base);
     cudaFree(lists);
+    cudaFree(rlists);
+    cudaFree(r_out);
     cudaFree(info_dev);
     cudaFree(tbuf);
     for (cudaEvent_t e : pev)
@@ -483,6 +494,9 @@ struct Plan final : dlafb_chol_plan {
       sc = t;
     }
     dist = P * Q > 1;
+    worldc = g->world;
+    src_r = sr;
+    src_c = sc;
     sched = make_schedule(n, nb, P, Q, pr, pc, sr, sc);
     nt = sched.rows.nt();
     mloc = sched.rows.local_size();
@@ -608,9 +622,10 @@ struct Plan final : dlafb_chol_plan {
   // serial chain of nb/16 slices, so 4x more, 4x shorter CTAs end the launch sooner (the look-ahead column and the
   // last steps are on the critical path).
   int update(cudaStream_t s, T* A, int64_t ld, const CUtensorMap* map_a_local, int nbox_local, int64_t k, int buf,
-             size_t off, size_t count, bool bulk = false, const int2* list_base = nullptr) {
+             size_t off, size_t count, bool bulk = false, const int2* list_base = nullptr, bool panels = false) {
     if (!list_base)
       list_base = lists;
+    panels = panels || dist;  // operands from the packed panels Pr / Pc (always when distributed)
     if (count == 0)
       return 0;
     if (fast) {
@@ -633,7 +648,7 @@ struct Plan final : dlafb_chol_plan {
       // step time: run it as one persistent CTA per SM on all SMs but one. Every high-priority kernel then finds a
       // free half SM at once, the single-CTA diagonal kernel a whole SM, instead of waiting for update CTAs to retire.
       const unsigned cap = (bulk && big < reserve_below()) ? (unsigned)std::max(1, gemm_sm_count() - 1) : 0u;
-      if (dist) {
+      if (panels) {
         p.nbox_a = p.nbox_b = 4;
         return (int)launch_gemm_nt_dmma(s, bm == 64 ? map_pr_s[buf] : map_pr[buf], bn == 64 ? map_pc_s[buf] : map_pc[buf],
                                         p, ctas, 1, shape, cplx, cap);
@@ -654,7 +669,7 @@ struct Plan final : dlafb_chol_plan {
     p.list = list_base + off;
     p.sub = (int)((nb + kSimtTile - 1) / kSimtTile);
     p.tile = (int)nb;
-    if (dist) {
+    if (panels) {
       p.A = Pr[buf];
       p.B = Pc[buf];
       p.lda = p.ldb = nb;
@@ -762,6 +777,120 @@ struct Plan final : dlafb_chol_plan {
                            (size_t)ldd * sizeof(T), (size_t)nr * sizeof(T), (size_t)nc, cudaMemcpyDeviceToHost, user));
       return 0;
     });
+  }
+
+  // Residual of a factorization, on the device and distributed like the matrix (the reference's checker,
+  // miniapp_cholesky.cpp:243-442, gathers norms on the CPU with blocking MPI and costs more than the factorization):
+  // R <- A0 - L*L^H by the same panel exchange and the same update kernels as the factorization (inclusive
+  // schedule, no diagonal-tile or solve kernels), then max|.| over the referenced triangle and a max-reduction over
+  // the grid. `r` holds this rank's block of the ORIGINAL matrix and is overwritten with the residual; `l` holds
+  // the factor. out2 = {max|A0|, max|A0 - L*L^H|}. uplo = Lower only. Synchronises `user` at the end.
+  int residual(void* r_, int64_t ldr, const void* l_, int64_t ldl, cudaStream_t user, double* out2) override {
+    if (upper)
+      return 2;
+    T* Rm = static_cast<T*>(r_);
+    const T* Lm = static_cast<const T*>(l_);
+    out2[0] = out2[1] = 0.0;
+    if (n <= 0)
+      return 0;
+    const size_t slot = (size_t)nb * nb;
+    if (!r_ready) {
+      rsched = make_schedule(n, nb, P, Q, pr, pc, src_r, src_c, true);
+      std::vector<int2> all;
+      r_off.assign((size_t)nt + 1, 0);
+      for (int64_t k = 0; k < nt; ++k) {
+        r_off[(size_t)k] = all.size();
+        for (const UpdateTile& t : rsched.steps[k].np)
+          all.push_back(make_int2(t.row, t.col | (t.diag ? (int)0x80000000 : 0)));
+      }
+      r_off[(size_t)nt] = all.size();
+      if (!all.empty()) {
+        CU(cudaMalloc(&rlists, all.size() * sizeof(int2)));
+        CU(cudaMemcpy(rlists, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
+      }
+      CU(cudaMalloc(&r_out, 2 * sizeof(double)));
+      if (!dist) {
+        // a single-rank plan factors out of the matrix itself; the checker needs packed panels (the diagonal tile
+        // enters with its strictly upper part zeroed)
+        CU(cudaMalloc(&Pr[0], (size_t)(nt + 1) * slot * sizeof(T)));
+        CU(cudaMemset(Pr[0], 0, (size_t)(nt + 1) * slot * sizeof(T)));
+        Pc[0] = Pr[0];
+        if (fast) {
+          const long long tr = (long long)nb * vs;
+          if (make_operand_map(&map_pr[0], (const double*)Pr[0], (long long)nt * tr, nb, tr, 4, 128, nb) != 0 ||
+              make_operand_map(&map_pr_s[0], (const double*)Pr[0], (long long)nt * tr, nb, tr, 4, 64, nb) != 0)
+            return -2;
+          map_pc[0] = map_pr[0];
+          map_pc_s[0] = map_pr_s[0];
+        }
+      }
+      r_ready = true;
+    }
+    const ncclDataType_t nt_ = NcclType<T>::t;
+    const size_t mult = NcclType<T>::mult;
+    CU(cudaEventRecord(ev_in, user));
+    CU(cudaStreamWaitEvent(hp, ev_in, 0));
+    CU(cudaMemsetAsync(r_out, 0, 2 * sizeof(double), hp));
+    // max over this rank's part of the lower triangle: the diagonal tile's lower part + everything below it
+    auto tri_max = [&](double* out) -> int {
+      for (int64_t jl = 0; jl < rsched.cols.nloc_tiles(); ++jl) {
+        const int64_t gj = rsched.cols.global_of(jl);
+        const int w = (int)rsched.cols.tile_size(gj);
+        int64_t il = rsched.rows.next_local(gj);
+        const T* col = Rm + (size_t)jl * nb * ldr;
+        if (il < rsched.rows.nloc_tiles() && rsched.rows.global_of(il) == gj) {
+          CU(max_abs<T>(hp, 'L', w, w, col + (size_t)il * nb, ldr, out));
+          ++il;
+        }
+        const int64_t r0 = il * nb;
+        if (r0 < mloc)
+          CU(max_abs<T>(hp, 'G', (int)(mloc - r0), w, col + r0, ldr, out));
+      }
+      return 0;
+    };
+    PP(tri_max(r_out));
+    for (int64_t k = 0; k < nt; ++k) {
+      const Step& st = rsched.steps[k];
+      const int w = (int)rsched.rows.tile_size(k);
+      const size_t row_cnt = (size_t)(st.il_end - st.il0) * slot;
+      if (st.in_col && row_cnt > 0) {
+        const int64_t r0 = (int64_t)st.il0 * nb;
+        T* dst = Pr[0] + (size_t)st.il0 * slot;
+        if (w < nb)
+          CU(cudaMemsetAsync(dst, 0, row_cnt * sizeof(T), hp));  // ragged last tile column: zero-padded to nb
+        CU(pack_tiles<T>(hp, (int)(mloc - r0), w, Lm + r0 + (size_t)st.lk_col * nb * ldl, ldl, dst, (int)nb));
+        if (st.own_diag && w > 1)  // strictly upper part of the diagonal tile = upper triangle of T[0:w-1, 1:w]
+          CU(laset<T>(hp, 'U', w - 1, w - 1, Tr<T>::zero(), Tr<T>::zero(), dst + nb, nb));
+      }
+      if (Q > 1 && row_cnt > 0) {
+        T* p = Pr[0] + (size_t)st.il0 * slot;
+        NC(ncclBroadcast(p, p, row_cnt * mult, nt_, st.row_root, rowc, hp));
+      }
+      if (P > 1 && !st.colb.empty()) {
+        NC(ncclGroupStart());
+        for (const ColBcast& cb : st.colb) {
+          T* recv = Pc[0] + (size_t)cb.jl * slot;
+          const T* send = (cb.root == pr) ? Pr[0] + (size_t)cb.src_il * slot : recv;
+          NC(ncclBroadcast(send, recv, slot * mult, nt_, cb.root, colc, hp));
+        }
+        NC(ncclGroupEnd());
+      }
+      else if (dist) {
+        for (const ColBcast& cb : st.colb)
+          CU(cudaMemcpyAsync(Pc[0] + (size_t)cb.jl * slot, Pr[0] + (size_t)cb.src_il * slot, slot * sizeof(T),
+                             cudaMemcpyDeviceToDevice, hp));
+      }
+      const int r = update(hp, Rm, ldr, nullptr, 1, k, 0, r_off[(size_t)k], r_off[(size_t)k + 1] - r_off[(size_t)k],
+                           false, rlists, true);
+      if (r != 0)
+        return r;
+    }
+    PP(tri_max(r_out + 1));
+    if (dist)
+      NC(ncclAllReduce(r_out, r_out, 2, ncclDouble, ncclMax, worldc, hp));
+    CU(cudaMemcpyAsync(out2, r_out, 2 * sizeof(double), cudaMemcpyDeviceToHost, hp));
+    CU(cudaStreamSynchronize(hp));
+    return 0;
   }
 
   int factor_lower(T* A, int64_t ld) {
@@ -1190,6 +1319,17 @@ int dlafb_cholesky_plan_set_profiling(dlafb_chol_plan_t plan, int on) {
     return -1;
   plan->profiling = on != 0;
   return 0;
+}
+
+int dlafb_cholesky_plan_residual(dlafb_chol_plan_t plan, void* a0, int64_t lda, const void* l, int64_t ldl, void* stream,
+                                 double* max_abs_a, double* max_abs_diff) {
+  if (!plan || !a0 || !l || !max_abs_a || !max_abs_diff)
+    return 1;
+  double out[2] = {0.0, 0.0};
+  const int r = plan->residual(a0, lda, l, ldl, static_cast<cudaStream_t>(stream), out);
+  *max_abs_a = out[0];
+  *max_abs_diff = out[1];
+  return r;
 }
 
 int dlafb_cholesky_plan_exchange_mode(dlafb_chol_plan_t plan) {

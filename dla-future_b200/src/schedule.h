@@ -68,7 +68,11 @@ struct Schedule {
   std::vector<Step> steps;
 };
 
-inline Schedule make_schedule(int64_t n, int64_t nb, int P, int Q, int pr, int pc, int sr, int sc) {
+// inclusive = false: the factorization (step k touches the tiles with global column > k).
+// inclusive = true: the residual A - L*L^H (step k subtracts L(:,k)*L(:,k)^H from every tile with column >= k, the
+// panel starts at the diagonal tile, there is no look-ahead list and the last step is a step like the others).
+inline Schedule make_schedule(int64_t n, int64_t nb, int P, int Q, int pr, int pc, int sr, int sc,
+                              bool inclusive = false) {
   Schedule s;
   s.rows = Dist1D{n, nb, P, pr, sr};
   s.cols = Dist1D{n, nb, Q, pc, sc};
@@ -87,11 +91,11 @@ inline Schedule make_schedule(int64_t n, int64_t nb, int P, int Q, int pr, int p
       st.lk_row = (int)R.local_of(k);
     if (st.in_col)
       st.lk_col = (int)C.local_of(k);
-    st.il0 = (int)R.next_local(k + 1);
-    st.jl0 = (int)C.next_local(k + 1);
+    st.il0 = (int)R.next_local(inclusive ? k : k + 1);
+    st.jl0 = (int)C.next_local(inclusive ? k : k + 1);
     st.il_end = (int)R.nloc_tiles();
     st.jl_end = (int)C.nloc_tiles();
-    if (k == nt - 1)
+    if (k == nt - 1 && !inclusive)
       continue;
     for (int jl = st.jl0; jl < st.jl_end; ++jl) {
       const int64_t g = C.global_of(jl);
@@ -111,7 +115,7 @@ inline Schedule make_schedule(int64_t n, int64_t nb, int P, int Q, int pr, int p
         for (int il = std::max((int)R.next_local(gj), ib0); il < ib1; ++il) {
           const int64_t gi = R.global_of(il);
           UpdateTile t{(int)(il * nb), (int)(jl * nb), gi == gj ? 1 : 0};
-          (gj == k + 1 ? st.hp : st.np).push_back(t);
+          (gj == k + 1 && !inclusive ? st.hp : st.np).push_back(t);
         }
       }
     }

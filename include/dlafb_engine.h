@@ -94,6 +94,14 @@ int dlafb_cholesky_plan_profile(dlafb_chol_plan_t plan, double* update_ms, doubl
  * updated (all on the high-priority stream), bulk update begin / end. -1 where not recorded. out holds >= 8*nt. */
 int dlafb_cholesky_plan_timeline(dlafb_chol_plan_t plan, double* out, long long cap);
 
+/* Residual check of a factorization on the device, distributed like the matrix (replaces the reference miniapp's
+ * CPU checker, miniapp/miniapp_cholesky.cpp:243-442: max|A - L L^H| / max|A| <= n*eps). `a0` = this rank's block
+ * of the ORIGINAL matrix (overwritten with the residual), `l` = the factor. Collective over the grid; uplo = L plans
+ * only (returns 2 otherwise). Returns the two maxima over the whole grid, taken over the referenced triangle.
+ * Synchronises. */
+int dlafb_cholesky_plan_residual(dlafb_chol_plan_t plan, void* a0, int64_t lda, const void* l, int64_t ldl, void* stream,
+                                 double* max_abs_a, double* max_abs_diff);
+
 /* How the panels travel between ranks: 0 = single rank, 1 = ncclBroadcast on row / column communicators,
  * 2 = copies into the peers' memory over NVLink (CUDA IPC, copy engines) with stream-ordered step counters; chosen at
  * plan creation (2 when every rank of the grid can map its row and column peers; DLAFB_P2P=0 forces 1). */

@@ -86,11 +86,33 @@ def main():
                     inf = plan.info()
                     torch.cuda.synchronize()
                     out = dev.cpu().numpy().reshape(host.shape)
+                    res_msg = ""
+                    if uplo == "L" and n > 0:
+                        # the distributed device-side residual check against numpy on the global matrix
+                        dev0 = torch.from_numpy(host.reshape(-1).copy()).cuda()
+                        amax, dmax = plan.residual(dev0.data_ptr(), ld, dev.data_ptr(), ld, stream)
+                        low = np.tril(np.ones((n, n), bool))
+                        want_amax = float(np.abs(a_glob[low]).max())
+                        eps_ = float(np.finfo(a_glob.dtype).eps)
+                        if abs(amax - want_amax) > 1e-6 * want_amax or not (dmax <= 8 * n * eps_ * want_amax):
+                            res_msg = f" residual amax={amax} (want {want_amax}) dmax={dmax}"
+                        # ... and it must see a wrong factor: perturb one local element of L on the owner of (0, 0)
+                        if len(rows) and len(cols) and rows[0] == 0 and cols[0] == 0:
+                            bad_l = dev.clone()
+                            bad_l[0] += 1.0
+                        else:
+                            bad_l = dev
+                        dev0 = torch.from_numpy(host.reshape(-1).copy()).cuda()
+                        _, dbad = plan.residual(dev0.data_ptr(), ld, bad_l.data_ptr(), ld, stream)
+                        if not (dbad > 0.5):
+                            res_msg += f" residual blind to a perturbed factor (dmax={dbad})"
                     plan.close()
                 got = np.ascontiguousarray(out[:len(cols), :len(rows)].T)
                 bad = orc.check_near(got, expect[np.ix_(rows, cols)], tol, tol) if got.size else 0
                 pad_ok = bool(np.all(out[:len(cols), len(rows):] == a_glob.dtype.type(-7.7)))
-                return (inf != 0) or bad > 0 or not pad_ok, f"{what} info={inf} bad={bad} pad_ok={pad_ok}"
+                res_msg = locals().get("res_msg", "")
+                return ((inf != 0) or bad > 0 or not pad_ok or bool(res_msg),
+                        f"{what} info={inf} bad={bad} pad_ok={pad_ok}{res_msg}")
 
             for x in TYPES:
                 for uplo in "LU":

@@ -163,3 +163,40 @@ def test_run_host_moves_only_the_referenced_triangle(pkg, L, uplo, n, nb):
     assert np.array_equal(pinned.numpy().T, got)
     plan.close()
     grid.close()
+
+
+@pytest.mark.parametrize("x,n,nb", [("d", 1536, 256), ("d", 1100, 128), ("d", 650, 128), ("z", 768, 128), ("s", 640, 64),
+                                    ("c", 300, 128), ("d", 34, 13)])
+def test_device_residual_matches_numpy(pkg, L, x, n, nb):
+    """dlafb_cholesky_plan_residual (the miniapp's acceptance check, on the device) against numpy: exact max|A| over
+    the lower triangle, max|A - L L^H| equal up to rounding, and sensitivity to a wrong factor."""
+    dt = NP[x]
+    a = orc.gen_hpd(n, nb, dt)
+    grid = pkg.Grid(L)
+    plan = pkg.CholeskyPlan(L, grid, x, "L", n, nb)
+    ld = -(-n // 64) * 64
+    A = DevMat(a, ld=ld)
+    plan.run(A.ptr, A.ld, stream_ptr())
+    assert plan.info() == 0
+    got = A.get()
+    A0 = DevMat(a, ld=ld)
+    amax, dmax = plan.residual(A0.ptr, A0.ld, A.ptr, A.ld, stream_ptr())
+    low = np.tril(np.ones((n, n), bool))
+    lf = np.tril(got).astype(np.complex128 if x in "cz" else np.float64)
+    want = np.abs((a.astype(lf.dtype) - lf @ lf.conj().T)[low]).max()
+    eps = np.finfo(dt).eps
+    assert amax == pytest.approx(np.abs(a[low]).max(), rel=1e-6)
+    assert dmax <= n * eps * amax                      # the reference's acceptance threshold
+    assert dmax == pytest.approx(want, rel=0.5, abs=4 * eps * amax)
+    # the residual block itself: R = A - L L^H on the referenced triangle
+    r = A0.get()
+    assert np.abs(r[low] - (a.astype(lf.dtype) - lf @ lf.conj().T)[low]).max() <= 16 * eps * amax
+    assert np.all(A0.pad() == dt(-7.7))
+    # a wrong factor is seen
+    bad = got.copy()
+    bad[n // 2, n // 3] += 1
+    B, A1 = DevMat(bad, ld=ld), DevMat(a, ld=ld)
+    _, dbad = plan.residual(A1.ptr, A1.ld, B.ptr, B.ld, stream_ptr())
+    assert dbad > 0.5
+    plan.close()
+    grid.close()
