@@ -8,7 +8,7 @@
 // style) and the ranks share the NCCL id through the file named by DLAFB_ID_FILE (default /tmp/dlafb_nccl_id).
 // Differences to the reference, all outside the timed region: the input is generated on the device by the
 // counter-based generator (same distribution of values as set_random_hermitian_positive_definite), and the
-// residual check runs on the GPU and only for single-rank runs.
+// residual check runs on the GPU; multi-rank runs use the engine's distributed checker (uplo = lower).
 #include <unistd.h>
 
 #include <chrono>
@@ -232,10 +232,37 @@ static void run(const Options& opts, int rank, int size) {
           std::cout << "Warning! At the moment result checking works just with block sizes dividing matrix size."
                     << std::endl;  // miniapp_cholesky.cpp:90-95
       }
-      else if (size > 1) {
+      else if (size > 1 && opts.uplo == blas::Uplo::Upper) {
         if (rank == 0)
-          std::cout << "check-result: distributed residual check not available in this build (single rank only)"
-                    << std::endl;
+          std::cout << "check-result: the distributed residual check covers uplo = lower only" << std::endl;
+      }
+      else if (size > 1) {
+        // distributed, on the device: A - L L^H through the engine's own exchange and update kernels
+        Matrix<T, Device::GPU> original(matrix_size, block_size, comm_grid);
+        generate(original, 42);
+        original.waitLocalTiles();
+        dlafb_chol_plan_t plan = nullptr;
+        double amax = 0, dmax = 0;
+        int e = dlafb_cholesky_plan_create(&plan, comm_grid.handle(), dlaf::internal::TypeCode<T>::value, 'L', opts.m,
+                                           opts.mb, 0, 0);
+        if (e == 0)
+          e = dlafb_cholesky_plan_residual(plan, original.ptr(), original.ld(), matrix.ptr(), matrix.ld(),
+                                           original.stream(), &amax, &dmax);
+        if (plan)
+          dlafb_cholesky_plan_destroy(plan);
+        if (rank == 0) {
+          const double diff = amax > 0 ? dmax / amax : 0.0;
+          const double eps = std::numeric_limits<BaseType<T>>::epsilon();
+          if (e != 0)
+            std::cout << "ERROR: residual check failed to run (" << e << ")" << std::endl;
+          else {
+            if (diff > 100 * eps * opts.m)
+              std::cout << "ERROR: ";
+            else if (diff > eps * opts.m)
+              std::cout << "Warning: ";
+            std::cout << "Max Diff / Max A: " << diff << std::endl;
+          }
+        }
       }
       else {
         Matrix<T, Device::GPU> original(matrix_size, block_size, comm_grid);
