@@ -444,3 +444,109 @@ def cholesky_local_threaded(uplo, a, nb, task_threads=None, blas_threads=1):
     n = a.shape[0]
     return getattr(L, f"oracle_cholesky_local_{_x(a.dtype)}")(uplo.encode(), n, nb, a.ctypes.data,
                                                               max(1, a.strides[1] // a.itemsize))
+
+
+# ----------------------------------------------------------------------------------------------
+# Triangular solver: the consumer of the Cholesky factor.
+#   analytical system   test/include/dlaf_test/matrix/util_generic_blas.h:235-371
+#   local algorithms    include/dlaf/solver/triangular/impl.h:235-470 (call_LLN ... call_RUT)
+#   test sizes/tolerance  test/unit/solver/test_triangular.cpp:57-106 (40 (m+1) err, alpha = (-1.2, .7))
+# ----------------------------------------------------------------------------------------------
+TRIANGULAR_TEST_SIZES = [  # (m, n, mb, nb), test_triangular.cpp:57-63
+    (0, 0, 1, 1), (0, 2, 1, 2), (7, 0, 2, 1), (2, 2, 5, 5), (10, 10, 2, 3), (7, 7, 3, 2), (3, 2, 7, 7), (12, 3, 5, 5),
+    (7, 6, 3, 2), (15, 7, 3, 5), (2, 3, 7, 7), (4, 13, 5, 5), (7, 8, 2, 9), (19, 25, 6, 5),
+]
+
+
+def triangular_test_alpha(dtype):
+    """TypeUtilities<T>::element(-1.2, .7): the imaginary part only exists for complex types."""
+    dtype = np.dtype(dtype)
+    return dtype.type(-1.2 + 0.7j) if dtype.kind == "c" else dtype.type(-1.2)
+
+
+def _polar(r, theta, dtype):
+    dtype = np.dtype(dtype)
+    return (r * np.exp(1j * theta)).astype(dtype) if dtype.kind == "c" else (r + 0 * theta).astype(dtype)
+
+
+def triangular_system(side, uplo, op, diag, alpha, m, n, dtype):
+    """getTriangularSystem: returns (A, B, X) with op(A) X = alpha B (side 'L') or X op(A) = alpha B ('R').
+
+    A is what the reference's `set(mat_a, el_op_a, op)` stores: A = el_op_a for 'N', its transpose for 'T', its
+    conjugate transpose for 'C'; elements outside the uplo triangle, and the diagonal when diag == 'U', are -9.9.
+    """
+    dtype = np.dtype(dtype)
+    op_a_lower = (uplo == "L") == (op == "N")
+    na = m if side == "L" else n
+    r = np.arange(na, dtype=np.float64)[:, None]
+    c = np.arange(na, dtype=np.float64)[None, :]
+    i = np.arange(m, dtype=np.float64)[:, None]
+    j = np.arange(n, dtype=np.float64)[None, :]
+    if side == "L":
+        op_a = _polar((r + 1) / (c + .5), 2 * r - c, dtype)
+        x = _polar((i + .5) / (j + 2), i + j, dtype)
+        kk = (i + 1) if op_a_lower else (m - i)
+        gamma = _polar((i + 1) / (j + 2), 2 * i + j, dtype)
+    else:
+        op_a = _polar((c + 1) / (r + .5), 2 * c - r, dtype)
+        x = _polar((j + .5) / (i + 2), i + j, dtype)
+        kk = (n - j) if op_a_lower else (j + 1)
+        gamma = _polar((j + 1) / (i + 2), i + 2 * j, dtype)
+    unref = (r < c) if op_a_lower else (r > c)
+    if diag == "U":
+        unref = unref | (r == c)
+    op_a = np.where(unref, dtype.type(-9.9), op_a)
+    kk = (kk + 0 * (i + j)).astype(dtype)
+    if diag == "U":
+        b = ((kk - 1) * gamma + x) / alpha
+    else:
+        b = kk * gamma / alpha
+    a = op_a if op == "N" else op_a.T if op == "T" else op_a.conj().T
+    return np.asfortranarray(a.astype(dtype)), np.asfortranarray(b.astype(dtype)), np.asfortranarray(x.astype(dtype))
+
+
+def _tile_trsm(side, uplo, op, diag, alpha, a, b):
+    """tile::trsm (blas/tile.h:359-366): b <- alpha op(a)^-1 b or alpha b op(a)^-1."""
+    if b.size:
+        b[...] = _f("trsm", b.dtype)(alpha, a, b, side=int(side == "R"), lower=int(uplo == "L"),
+                                     trans_a={"N": 0, "T": 1, "C": 2}[op], diag=int(diag == "U"))
+
+
+def _opm(a, op):
+    return a if op == "N" else a.T if op == "T" else a.conj().T
+
+
+def triangular_solver_local(side, uplo, op, diag, alpha, a, b, mb, nb):
+    """In-place tiled solve of op(A) X = alpha B / X op(A) = alpha B following the eight local loops of
+    solver/triangular/impl.h:235-470: per step a tile trsm with `alpha` on the k-th panel of B, then tile gemms with
+    beta = -1/alpha on the tiles still to be solved. A has (mb x mb) tiles for side 'L', (nb x nb) for 'R'."""
+    m, n = b.shape
+    mt = -(-m // mb) if m else 0
+    nt = -(-n // nb) if n else 0
+    alpha = b.dtype.type(alpha)
+    beta = b.dtype.type(-1.0) / alpha
+    ab = mb if side == "L" else nb
+    ta = lambda i, j: a[i * ab:(i + 1) * ab, j * ab:(j + 1) * ab]
+    tb = lambda i, j: b[i * mb:(i + 1) * mb, j * nb:(j + 1) * nb]
+    forward = {("L", "L", "N"): True, ("L", "L", "T"): False, ("L", "U", "N"): False, ("L", "U", "T"): True,
+               ("R", "L", "N"): False, ("R", "L", "T"): True, ("R", "U", "N"): True, ("R", "U", "T"): False}[
+        (side, uplo, "N" if op == "N" else "T")]
+    if side == "L":
+        order = range(mt) if forward else range(mt - 1, -1, -1)
+        for k in order:
+            rest = range(k + 1, mt) if forward else range(k - 1, -1, -1)
+            for j in range(nt):
+                _tile_trsm(side, uplo, op, diag, alpha, ta(k, k), tb(k, j))
+                for i in rest:
+                    aik = ta(i, k) if op == "N" else _opm(ta(k, i), op)
+                    tb(i, j)[...] += beta * (aik @ tb(k, j))
+    else:
+        order = range(nt) if forward else range(nt - 1, -1, -1)
+        for k in order:
+            rest = range(k + 1, nt) if forward else range(k - 1, -1, -1)
+            for i in range(mt):
+                _tile_trsm(side, uplo, op, diag, alpha, ta(k, k), tb(i, k))
+                for j in rest:
+                    akj = ta(k, j) if op == "N" else _opm(ta(j, k), op)
+                    tb(i, j)[...] += beta * (tb(i, k) @ akj)
+    return b
