@@ -2,6 +2,7 @@
 #   make            -> dla-future_b200/lib/libdlaf_b200.so
 #   make miniapp    -> dla-future_b200/bin/miniapp_cholesky
 #   make oracle     -> oracle/_build/liboracle.so (test infrastructure only)
+#   make emu        -> tests/emu/_build/libsolver_emu.so (test infrastructure only)
 NVCC      ?= /usr/local/cuda/bin/nvcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 PKG       := dla-future_b200
@@ -39,7 +40,14 @@ oracle:
 	@mkdir -p oracle/_build
 	g++ -O2 -fopenmp -shared -fPIC -o oracle/_build/liboracle.so oracle/chol_oracle.cpp -ldl
 
-clean:
-	rm -rf $(BUILD) $(LIBDIR) $(BINDIR)
+# CPU execution of the triangular solver's algorithm template and kernel bodies (test infrastructure only)
+emu: tests/emu/_build/libsolver_emu.so
 
-.PHONY: all miniapp oracle clean
+tests/emu/_build/libsolver_emu.so: tests/emu/solver_emu.cu $(SRC)/triangular_solver.h $(CSRC)/solver_kernels.cuh $(CSRC)/common.cuh
+	@mkdir -p tests/emu/_build
+	$(NVCC) -O2 -std=c++17 -Wno-deprecated-gpu-targets -shared -Xcompiler -fPIC -I$(CSRC) -I$(SRC) -o $@ $<
+
+clean:
+	rm -rf $(BUILD) $(LIBDIR) $(BINDIR) tests/emu/_build
+
+.PHONY: all miniapp oracle emu clean

@@ -1,5 +1,5 @@
-"""ctypes signatures of include/dlafb_engine.h plus thin Python wrappers (Grid, CholeskyPlan) used by the tests
-and by bench.py. No arithmetic happens here."""
+"""ctypes signatures of include/dlafb_engine.h and include/dlafb_solver.h plus thin Python wrappers (Grid,
+CholeskyPlan, TriangularSolverPlan) used by the tests and by bench.py. No arithmetic happens here."""
 import ctypes
 
 c_i64 = ctypes.c_int64
@@ -46,6 +46,12 @@ ENGINE_API = {
     "dlafb_cholesky_plan_exchange_mode": (c_int, [c_vp]),
     "dlafb_cholesky_plan_residual": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, P_dbl, P_dbl]),
     "dlafb_launch_count": (ctypes.c_uint64, []),
+    # include/dlafb_solver.h
+    "dlafb_triangular_solver_plan_create": (c_int, [ctypes.POINTER(c_vp), c_char, c_char, c_char, c_char, c_char, c_i64,
+                                                    c_i64, c_i64]),
+    "dlafb_triangular_solver_plan_run": (c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
+    "dlafb_triangular_solver_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
+    "dlafb_triangular_solver_plan_destroy": (c_int, [c_vp]),
 }
 
 
@@ -154,4 +160,32 @@ class CholeskyPlan:
     def close(self):
         if self.h:
             self.L.dlafb_cholesky_plan_destroy(self.h)
+            self.h = c_vp()
+
+
+_CTYPE = {"s": ctypes.c_float * 1, "d": ctypes.c_double * 1, "c": ctypes.c_float * 2, "z": ctypes.c_double * 2}
+
+
+class TriangularSolverPlan:
+    """dlaf::triangular_solver on one GPU (include/dlafb_solver.h): op(A) X = alpha B or X op(A) = alpha B."""
+
+    def __init__(self, L, type_, side, uplo, op, diag, m, n, nb):
+        self.L = L
+        self.type = type_
+        self.h = c_vp()
+        _ck(L.dlafb_triangular_solver_plan_create(ctypes.byref(self.h), type_.encode(), side.encode(), uplo.encode(),
+                                                  op.encode(), diag.encode(), m, n, nb), "triangular_solver_plan_create")
+
+    def run(self, alpha, a_ptr, lda, b_ptr, ldb, stream):
+        al = complex(alpha)
+        buf = _CTYPE[self.type](al.real, al.imag) if self.type in "cz" else _CTYPE[self.type](al.real)
+        _ck(self.L.dlafb_triangular_solver_plan_run(self.h, ctypes.addressof(buf), a_ptr, lda, b_ptr, ldb, stream),
+            "triangular_solver_plan_run")
+
+    def workspace_bytes(self):
+        return self.L.dlafb_triangular_solver_plan_workspace_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.dlafb_triangular_solver_plan_destroy(self.h)
             self.h = c_vp()

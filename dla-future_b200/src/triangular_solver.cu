@@ -1,0 +1,136 @@
+// Device executor and C ABI of the local triangular solver (algorithm: triangular_solver.h).
+#include "triangular_solver.h"
+
+#include <cuda_runtime.h>
+
+#include <new>
+
+#include "dlafb_solver.h"
+#include "tile_ops.cuh"
+
+namespace dlafb {
+namespace {
+
+// Everything is enqueued on one stream, in program order.
+template <class T>
+struct DeviceOps {
+  cudaStream_t s;
+  using R = typename Tr<T>::Real;
+  int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
+              long long ldc) {
+    return (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, 0);
+  }
+  int transpose(int m, int n, const T* in, long long ldin, T* out, long long ldout, int conj, char tri) {
+    return (int)dlafb::transpose<T>(s, m, n, in, ldin, out, ldout, conj, tri);
+  }
+  int lacpy(int m, int n, const T* a, long long lda, T* b, long long ldb) {
+    return (int)dlafb::lacpy<T>(s, 'G', m, n, a, lda, b, ldb);
+  }
+  int tri_inverse(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w) {
+    TriInvParams p{n, nb, ldt, upper, unit};
+    return (int)launch_tri_inverse<T>(s, p, t, w);
+  }
+  int scale(int m, int n, T* b, long long ldb, T alpha, int conj) {
+    return (int)launch_scale<T>(s, m, n, b, ldb, alpha, conj);
+  }
+};
+
+struct Plan {
+  char type;
+  TriSolveDesc d;
+  size_t elem;
+  void* tcopy = nullptr;
+  void* winv = nullptr;
+  void* panel = nullptr;
+  size_t bytes = 0;
+  ~Plan() {
+    cudaFree(tcopy);
+    cudaFree(winv);
+    cudaFree(panel);
+  }
+};
+
+template <class T>
+int run_typed(Plan& p, const void* alpha, const void* a, long long lda, void* b, long long ldb, cudaStream_t s) {
+  DeviceOps<T> ops{s};
+  TriSolveWork<T> w{static_cast<T*>(p.tcopy), tri_solve_ldt(p.d), static_cast<T*>(p.winv), static_cast<T*>(p.panel),
+                    tri_solve_ldp(p.d)};
+  return triangular_solve<T>(ops, p.d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda,
+                             static_cast<T*>(b), ldb, w);
+}
+
+bool one_of(char c, const char* set) {
+  for (; *set; ++set)
+    if (*set == c)
+      return true;
+  return false;
+}
+
+}  // namespace
+}  // namespace dlafb
+
+using namespace dlafb;
+
+extern "C" {
+
+int dlafb_triangular_solver_plan_create(dlafb_trsolve_plan_t* out, char type, char side, char uplo, char op, char diag,
+                                        int64_t m, int64_t n, int64_t nb) {
+  if (!out || !one_of(type, "sdcz") || !one_of(side, "LR") || !one_of(uplo, "LU") || !one_of(op, "NTC") ||
+      !one_of(diag, "NU") || m < 0 || n < 0 || nb < 1 || m > (1LL << 30) || n > (1LL << 30) || nb > (1 << 14))
+    return -1;
+  Plan* p = new (std::nothrow) Plan;
+  if (!p)
+    return (int)cudaErrorMemoryAllocation;
+  p->type = type;
+  p->d = TriSolveDesc{side, uplo, op, diag, (int)m, (int)n, (int)nb};
+  p->elem = type == 's' ? 4 : type == 'z' ? 16 : 8;
+  const size_t bt = tri_solve_tcopy_elems(p->d) * p->elem;
+  const size_t bw = tri_solve_winv_elems(p->d) * p->elem;
+  const size_t bp = tri_solve_panel_elems(p->d) * p->elem;
+  cudaError_t e = cudaSuccess;
+  if (m > 0 && n > 0) {
+    if (bt && e == cudaSuccess)
+      e = cudaMalloc(&p->tcopy, bt);
+    if (e == cudaSuccess)
+      e = cudaMalloc(&p->winv, bw);
+    if (e == cudaSuccess)
+      e = cudaMalloc(&p->panel, bp);
+    p->bytes = bt + bw + bp;
+  }
+  if (e != cudaSuccess) {
+    delete p;
+    return (int)e;
+  }
+  *out = reinterpret_cast<dlafb_trsolve_plan_t>(p);
+  return 0;
+}
+
+int dlafb_triangular_solver_plan_run(dlafb_trsolve_plan_t plan, const void* alpha, const void* a, int64_t lda, void* b,
+                                     int64_t ldb, void* stream) {
+  Plan* p = reinterpret_cast<Plan*>(plan);
+  if (!p || !alpha)
+    return -1;
+  if (p->d.m == 0 || p->d.n == 0)
+    return 0;
+  const int64_t order = tri_solve_order(p->d);
+  if (!a || !b || lda < order || ldb < p->d.m)
+    return -1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->type) {
+    case 's': return run_typed<float>(*p, alpha, a, lda, b, ldb, s);
+    case 'd': return run_typed<double>(*p, alpha, a, lda, b, ldb, s);
+    case 'c': return run_typed<float2>(*p, alpha, a, lda, b, ldb, s);
+    default: return run_typed<double2>(*p, alpha, a, lda, b, ldb, s);
+  }
+}
+
+size_t dlafb_triangular_solver_plan_workspace_bytes(dlafb_trsolve_plan_t plan) {
+  return plan ? reinterpret_cast<Plan*>(plan)->bytes : 0;
+}
+
+int dlafb_triangular_solver_plan_destroy(dlafb_trsolve_plan_t plan) {
+  delete reinterpret_cast<Plan*>(plan);
+  return 0;
+}
+
+}  // extern "C"

@@ -70,4 +70,7 @@ struct TypeCode<std::complex<double>> { static constexpr char value = 'z'; };
 
 namespace blas {
 enum class Uplo : char { Upper = 'U', Lower = 'L', General = 'G' };
+enum class Side : char { Left = 'L', Right = 'R' };
+enum class Op : char { NoTrans = 'N', Trans = 'T', ConjTrans = 'C' };
+enum class Diag : char { NonUnit = 'N', Unit = 'U' };
 }
