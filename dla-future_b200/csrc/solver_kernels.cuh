@@ -11,6 +11,13 @@
 
 #include "common.cuh"
 
+// the host pass of these __host__ __device__ bodies does not know the pragma
+#ifdef __CUDA_ARCH__
+#define DLAFB_UNROLL _Pragma("unroll")
+#else
+#define DLAFB_UNROLL
+#endif
+
 namespace dlafb {
 
 constexpr int kTriInvThreads = 256;  // threads per CTA of tri_inverse: thread t owns columns t, t + 256, ...
@@ -54,15 +61,27 @@ struct TriInvParams {
   int unit;        // 1: the diagonal is not referenced and taken as 1
 };
 
+// Rows of a column that one thread keeps in registers at a time (tri_inverse_body).
+template <class T>
+struct TriInvChunk {
+  static constexpr int value = Tr<T>::is_complex ? 16 : 32;
+};
+
 // W_b (nb x nb slot, leading dimension nb, at w + b*nb*nb) <- inv(T_bb), the other triangle of the w x w block set
-// to zero (the contraction kernel reads the full block). Column-wise substitution, one column per thread at a time:
-//   x_jj = 1 / t_jj,   x_ij = -(sum_{k=j}^{i-1} t_ik x_kj) / t_ii   (i > j)
-// for a lower tile; an upper tile is the same recurrence on the index-reversed tile (reversing rows and columns of
-// an upper triangular matrix gives a lower triangular one whose inverse is the reversed inverse).
+// to zero (the contraction kernel reads the full block). One column of the inverse per thread at a time, by forward
+// substitution on T x = e_j, R = TriInvChunk rows at a time held in registers:
+//   acc_r  = (e_j)_i - sum_{k < chunk} t_ik x_k     i = chunk*R + r; t_ik for the R rows of a chunk is contiguous
+//                                                   (column k of T) and the same address in every lane of a warp
+//   then the R x R triangle of the chunk is solved in registers and the chunk is written once.
+// (The first version formed each x_i as a dot product along ROW i of T: one 8-byte load per 32-byte sector, every
+// load an L2 round trip - 25 ms for 512 x 512 tiles, 15 % of a whole solve at n = 16384; profiles/r01/
+// trsolve_bench_v2_lookahead.jsonl.) An upper tile is the same recurrence on the index-reversed tile (reversing
+// rows and columns of an upper triangular matrix gives a lower triangular one whose inverse is the reversed inverse).
 template <class T>
 __host__ __device__ inline void tri_inverse_body(const TriInvParams p, const T* __restrict__ t, T* __restrict__ w,
                                                  int block, int thread, int nthreads) {
   using R = typename Tr<T>::Real;
+  constexpr int RC = TriInvChunk<T>::value;
   const int k0 = block * p.nb;
   const int order = p.n - k0 < p.nb ? p.n - k0 : p.nb;
   if (order <= 0)
@@ -70,31 +89,58 @@ __host__ __device__ inline void tri_inverse_body(const TriInvParams p, const T* 
   const T* tb = t + k0 + (long long)k0 * p.ldt;
   T* wb = w + (size_t)block * p.nb * p.nb;
   const int last = order - 1;
-  // position of logical index a (lower-triangular numbering) in storage
-  auto at = [&](int a) { return p.upper ? last - a : a; };
+  const int upper = p.upper;
+  // storage position of logical index a (logical = lower-triangular numbering)
+  auto at = [&](int a) { return upper ? last - a : a; };
+  // logical rows i0 .. i0 + RC - 1 of logical column k of T are contiguous in storage: ascending for a lower tile,
+  // descending for an upper one
+  const int dir = upper ? -1 : 1;
+  const int nchunks = ceil_div(order, RC);
   for (int j = thread; j < order; j += nthreads) {
     T* xcol = wb + (size_t)at(j) * p.nb;  // column j of the (reversed) inverse
-    for (int i = 0; i < j; ++i)
+    const int c_first = j / RC;
+    for (int i = 0; i < c_first * RC; ++i)
       xcol[at(i)] = Tr<T>::zero();
-    const T djj = p.unit ? Tr<T>::from_real(R(1)) : tr_recip<T>(tb[at(j) + (long long)at(j) * p.ldt]);
-    xcol[at(j)] = djj;
-    for (int i = j + 1; i < order; ++i) {
-      const T* trow = tb + at(i);  // t(i, k) = trow[at(k) * ldt]
-      T s0 = Tr<T>::zero(), s1 = Tr<T>::zero(), s2 = Tr<T>::zero(), s3 = Tr<T>::zero();
-      int k = j;
-      for (; k + 3 < i; k += 4) {
-        s0 = Tr<T>::fma(trow[(long long)at(k) * p.ldt], xcol[at(k)], s0);
-        s1 = Tr<T>::fma(trow[(long long)at(k + 1) * p.ldt], xcol[at(k + 1)], s1);
-        s2 = Tr<T>::fma(trow[(long long)at(k + 2) * p.ldt], xcol[at(k + 2)], s2);
-        s3 = Tr<T>::fma(trow[(long long)at(k + 3) * p.ldt], xcol[at(k + 3)], s3);
+    for (int c = c_first; c < nchunks; ++c) {
+      const int i0 = c * RC;
+      const int rows = order - i0 < RC ? order - i0 : RC;  // rows of this chunk inside the tile
+      T acc[RC];
+DLAFB_UNROLL
+      for (int r = 0; r < RC; ++r)
+        acc[r] = (i0 + r == j) ? Tr<T>::from_real(R(1)) : Tr<T>::zero();
+      // entries of this column solved in earlier chunks
+      for (int k = c_first * RC; k < i0; ++k) {
+        const T xk = xcol[at(k)];
+        const T* tcol = tb + at(i0) + (long long)at(k) * p.ldt;  // t(i0 + r, k) = tcol[dir * r]
+        if (rows == RC) {
+DLAFB_UNROLL
+          for (int r = 0; r < RC; ++r)
+            acc[r] = Tr<T>::fnma(tcol[dir * r], xk, acc[r]);
+        }
+        else {
+DLAFB_UNROLL
+          for (int r = 0; r < RC; ++r)
+            if (r < rows)
+              acc[r] = Tr<T>::fnma(tcol[dir * r], xk, acc[r]);
+        }
       }
-      for (; k < i; ++k)
-        s0 = Tr<T>::fma(trow[(long long)at(k) * p.ldt], xcol[at(k)], s0);
-      T s = Tr<T>::add(Tr<T>::add(s0, s1), Tr<T>::add(s2, s3));
-      s = tr_neg<T>(s);
-      if (!p.unit)
-        s = Tr<T>::mul(s, tr_recip<T>(trow[(long long)at(i) * p.ldt]));
-      xcol[at(i)] = s;
+      // the chunk's own triangle, in registers
+DLAFB_UNROLL
+      for (int r = 0; r < RC; ++r) {
+        if (r < rows) {
+          const T* tcol = tb + at(i0) + (long long)at(i0 + r) * p.ldt;  // t(i0 + r2, i0 + r) = tcol[dir * r2]
+          if (!p.unit)
+            acc[r] = Tr<T>::mul(acc[r], tr_recip<T>(tcol[dir * r]));
+DLAFB_UNROLL
+          for (int r2 = r + 1; r2 < RC; ++r2)
+            if (r2 < rows)
+              acc[r2] = Tr<T>::fnma(tcol[dir * r2], acc[r], acc[r2]);
+        }
+      }
+DLAFB_UNROLL
+      for (int r = 0; r < RC; ++r)
+        if (r < rows)
+          xcol[at(i0 + r)] = acc[r];
     }
   }
 }

@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <new>
 
 #include "dlafb_solver.h"
@@ -11,11 +12,17 @@
 namespace dlafb {
 namespace {
 
-// Everything is enqueued on one stream, in program order.
+// Operations go to the current lane's stream in program order; without look-ahead there is one lane, the caller's
+// stream.
 template <class T>
 struct DeviceOps {
   cudaStream_t s;
+  cudaStream_t lanes[2];
+  cudaEvent_t* events;
   using R = typename Tr<T>::Real;
+  void lane(int l) { s = lanes[l]; }
+  int signal(int ev) { return (int)cudaEventRecord(events[ev], s); }
+  int wait(int ev) { return (int)cudaStreamWaitEvent(s, events[ev], 0); }
   int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
               long long ldc) {
     return (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, 0);
@@ -35,6 +42,9 @@ struct DeviceOps {
   }
 };
 
+// Look-ahead on two streams (DLAFB_TRSOLVE_LOOKAHEAD=0/1 overrides).
+constexpr int kDefaultLookahead = 0;
+
 struct Plan {
   char type;
   TriSolveDesc d;
@@ -43,7 +53,27 @@ struct Plan {
   void* winv = nullptr;
   void* panel = nullptr;
   size_t bytes = 0;
+  // look-ahead: lane 0 = high-priority stream (block solves), lane 1 = bulk updates
+  int lookahead = 0;
+  cudaStream_t hp = nullptr, np = nullptr;
+  cudaEvent_t ev[kTriSolveEvents] = {};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   ~Plan() {
+    if (hp)
+      cudaStreamSynchronize(hp);
+    if (np)
+      cudaStreamSynchronize(np);
+    for (cudaEvent_t e : ev)
+      if (e)
+        cudaEventDestroy(e);
+    if (ev_fork)
+      cudaEventDestroy(ev_fork);
+    if (ev_join)
+      cudaEventDestroy(ev_join);
+    if (hp)
+      cudaStreamDestroy(hp);
+    if (np)
+      cudaStreamDestroy(np);
     cudaFree(tcopy);
     cudaFree(winv);
     cudaFree(panel);
@@ -52,11 +82,28 @@ struct Plan {
 
 template <class T>
 int run_typed(Plan& p, const void* alpha, const void* a, long long lda, void* b, long long ldb, cudaStream_t s) {
-  DeviceOps<T> ops{s};
   TriSolveWork<T> w{static_cast<T*>(p.tcopy), tri_solve_ldt(p.d), static_cast<T*>(p.winv), static_cast<T*>(p.panel),
                     tri_solve_ldp(p.d)};
-  return triangular_solve<T>(ops, p.d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda,
-                             static_cast<T*>(b), ldb, w);
+  if (!p.lookahead) {
+    DeviceOps<T> ops{s, {s, s}, p.ev};
+    return triangular_solve<T>(ops, p.d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda,
+                               static_cast<T*>(b), ldb, w);
+  }
+  w.lookahead = 1;
+  w.panel_stride = tri_solve_panel_elems(p.d);
+  // fork from the caller's stream, join back into it
+  cudaError_t ce;
+  if ((ce = cudaEventRecord(p.ev_fork, s)) != cudaSuccess || (ce = cudaStreamWaitEvent(p.hp, p.ev_fork, 0)) != cudaSuccess)
+    return (int)ce;
+  DeviceOps<T> ops{p.hp, {p.hp, p.np}, p.ev};
+  const int e = triangular_solve<T>(ops, p.d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda,
+                                    static_cast<T*>(b), ldb, w);
+  // join even after an error so that the caller's stream stays ordered after whatever was enqueued
+  cudaEventRecord(p.ev_join, p.np);
+  cudaStreamWaitEvent(p.hp, p.ev_join, 0);
+  cudaEventRecord(p.ev_join, p.hp);
+  cudaStreamWaitEvent(s, p.ev_join, 0);
+  return e;
 }
 
 bool one_of(char c, const char* set) {
@@ -86,8 +133,23 @@ int dlafb_triangular_solver_plan_create(dlafb_trsolve_plan_t* out, char type, ch
   p->elem = type == 's' ? 4 : type == 'z' ? 16 : 8;
   const size_t bt = tri_solve_tcopy_elems(p->d) * p->elem;
   const size_t bw = tri_solve_winv_elems(p->d) * p->elem;
-  const size_t bp = tri_solve_panel_elems(p->d) * p->elem;
+  const char* la = getenv("DLAFB_TRSOLVE_LOOKAHEAD");
+  p->lookahead = la ? (la[0] != '0') : kDefaultLookahead;
+  const size_t bp = tri_solve_panel_elems(p->d) * p->elem * (p->lookahead ? 2 : 1);
   cudaError_t e = cudaSuccess;
+  if (m > 0 && n > 0 && p->lookahead) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    e = cudaStreamCreateWithPriority(&p->hp, cudaStreamNonBlocking, hi);
+    if (e == cudaSuccess)
+      e = cudaStreamCreateWithPriority(&p->np, cudaStreamNonBlocking, lo);
+    for (int i = 0; i < kTriSolveEvents && e == cudaSuccess; ++i)
+      e = cudaEventCreateWithFlags(&p->ev[i], cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+  }
   if (m > 0 && n > 0) {
     if (bt && e == cudaSuccess)
       e = cudaMalloc(&p->tcopy, bt);

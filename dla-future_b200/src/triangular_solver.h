@@ -27,8 +27,17 @@
 // of the solve is a contraction; alpha is applied to B once at the start (the reference applies it in every tile
 // trsm and compensates with beta = -1/alpha in the gemms: same result).
 //
+// Look-ahead (TriSolveWork::lookahead): two lanes (streams). Lane 0 solves block s and applies its update to the
+// NEXT block only, lane 1 applies it to all the other remaining blocks ("bulk"), so that the solve of block s+1 -
+// a chain of small dependent launches - runs under the bulk update of step s instead of after it:
+//   lane 0:  solve(s) -> [bulk(s-1) done] update next(s) -> solve(s+1) -> ...
+//   lane 1:  bulk(s-1) -> [solve(s) done] bulk(s) -> ...
+// bulk(s-1) also writes the block that next(s) writes, hence the wait; the panel with X_s^H is double-buffered.
+//
 // The algorithm is a template over the executor `Ops` so that tests/emu/ can run the very same sequence of
-// operations, pointer arithmetic included, on the CPU (the device executor is in triangular_solver.cu).
+// operations, pointer arithmetic included, on the CPU (the device executor is in triangular_solver.cu); the CPU
+// executor also replays the two lanes under adversarial interleavings and checks every pair of operations that the
+// events leave unordered for overlapping reads / writes.
 #pragma once
 #include <cstddef>
 
@@ -48,9 +57,14 @@ struct TriSolveWork {
   T* tcopy;        // order x order (leading dimension ldt) when tri_solve_needs_copy(), else unused
   long long ldt;
   T* winv;         // ceil(order / nb) slots of nb x nb
-  T* panel;        // ldp x nb
+  T* panel;        // ldp x nb (two of them, panel_stride apart, with look-ahead)
   long long ldp;   // >= max(m, n)
+  int lookahead = 0;
+  size_t panel_stride = 0;
 };
+
+// events of the look-ahead variant (Ops::signal / Ops::wait)
+enum TriSolveEvent { kEvPrologue = 0, kEvSolve0 = 1, kEvSolve1 = 2, kEvBulk0 = 3, kEvBulk1 = 4, kTriSolveEvents = 5 };
 
 inline int tri_solve_order(const TriSolveDesc& d) { return d.side == 'L' ? d.m : d.n; }
 
@@ -79,6 +93,10 @@ inline size_t tri_solve_panel_elems(const TriSolveDesc& d) { return (size_t)tri_
 //   lacpy(m, n, a, lda, b, ldb)                             b <- a
 //   tri_inverse(upper, unit, n, nb, t, ldt, w)              w slots <- inverses of the diagonal tiles of t
 //   scale(m, n, b, ldb, alpha, conj)                        b <- alpha * (conj ? conj(b) : b)
+// and, used only with look-ahead:
+//   lane(l)      following operations go to lane l (0 or 1); each lane runs its operations in order
+//   signal(ev)   the current lane records event ev
+//   wait(ev)     the current lane waits for the last signal of ev enqueued so far (no-op if there is none)
 template <class T, class Ops>
 int triangular_solve(Ops& ops, const TriSolveDesc& d, T alpha, const T* A, long long lda, T* B, long long ldb,
                      const TriSolveWork<T>& w) {
@@ -113,6 +131,84 @@ int triangular_solve(Ops& ops, const TriSolveDesc& d, T alpha, const T* A, long 
     return e;
 
   const int nt = ceil_div(order, nb);
+  if (w.lookahead) {
+    if ((e = ops.signal(kEvPrologue)) != 0)
+      return e;
+    ops.lane(1);
+    if ((e = ops.wait(kEvPrologue)) != 0)
+      return e;
+    ops.lane(0);
+    bool bulk_issued[2] = {false, false};
+    for (int s = 0; s < nt; ++s) {
+      const int k = lower ? s : nt - 1 - s;
+      const int k0 = k * nb;
+      const int wk = order - k0 < nb ? order - k0 : nb;
+      const T* wkk = w.winv + (size_t)k * nb * nb;
+      T* pan = w.panel + (size_t)(s & 1) * w.panel_stride;
+      const bool more = s + 1 < nt;
+      // next block in solve order and what is left beyond it
+      const int kn = lower ? k + 1 : k - 1;
+      const int n0 = more ? kn * nb : 0;
+      const int wn = more ? (order - n0 < nb ? order - n0 : nb) : 0;
+      const int b0 = lower ? n0 + wn : 0;                            // first row / column of the bulk range
+      const int bulk = more ? (lower ? order - n0 - wn : n0) : 0;    // its extent
+      // ---- lane 0: solve block k
+      if (!left) {
+        T* bk = B + (long long)k0 * ldb;
+        if ((e = ops.lacpy(d.m, wk, bk, ldb, pan, w.ldp)) != 0)
+          return e;
+        if ((e = ops.gemm_nt(d.m, wk, wk, R(1), pan, w.ldp, wkk, (long long)nb, R(0), bk, ldb)) != 0)
+          return e;
+      }
+      else {
+        T* bk = B + k0;
+        if ((e = ops.transpose(wk, d.n, bk, ldb, pan, w.ldp, 1, 'G')) != 0)
+          return e;
+        if ((e = ops.gemm_nt(wk, d.n, wk, R(1), wkk, (long long)nb, pan, w.ldp, R(0), bk, ldb)) != 0)
+          return e;
+        if (more && (e = ops.transpose(wk, d.n, bk, ldb, pan, w.ldp, 1, 'G')) != 0)
+          return e;
+      }
+      if (!more)
+        break;
+      if ((e = ops.signal(kEvSolve0 + (s & 1))) != 0)
+        return e;
+      // ---- lane 0: update of the next block; bulk(s-1) wrote that block too
+      if (s >= 1 && bulk_issued[(s - 1) & 1] && (e = ops.wait(kEvBulk0 + ((s - 1) & 1))) != 0)
+        return e;
+      if (!left)
+        e = ops.gemm_nt(d.m, wn, wk, R(-1), B + (long long)k0 * ldb, ldb, t + n0 + (long long)k0 * ldt, ldt, R(1),
+                        B + (long long)n0 * ldb, ldb);
+      else
+        e = ops.gemm_nt(wn, d.n, wk, R(-1), t + n0 + (long long)k0 * ldt, ldt, pan, w.ldp, R(1), B + n0, ldb);
+      if (e != 0)
+        return e;
+      // ---- lane 1: all the other remaining blocks
+      bulk_issued[s & 1] = bulk > 0;
+      if (bulk > 0) {
+        ops.lane(1);
+        if ((e = ops.wait(kEvSolve0 + (s & 1))) != 0)
+          return e;
+        if (!left)
+          e = ops.gemm_nt(d.m, bulk, wk, R(-1), B + (long long)k0 * ldb, ldb, t + b0 + (long long)k0 * ldt, ldt, R(1),
+                          B + (long long)b0 * ldb, ldb);
+        else
+          e = ops.gemm_nt(bulk, d.n, wk, R(-1), t + b0 + (long long)k0 * ldt, ldt, pan, w.ldp, R(1), B + b0, ldb);
+        if (e != 0)
+          return e;
+        if ((e = ops.signal(kEvBulk0 + (s & 1))) != 0)
+          return e;
+        ops.lane(0);
+      }
+    }
+    // join: everything lane 1 did is ordered before what follows on lane 0
+    for (int q = 0; q < 2; ++q)
+      if (bulk_issued[q] && (e = ops.wait(kEvBulk0 + q)) != 0)
+        return e;
+    if (conj_b)
+      return ops.scale(d.m, d.n, B, ldb, Tr<T>::from_real(R(1)), 1);
+    return 0;
+  }
   for (int s = 0; s < nt; ++s) {
     const int k = lower ? s : nt - 1 - s;  // forward for a lower T, backward for an upper one
     const int k0 = k * nb;

@@ -2,9 +2,10 @@
 miniapp_triangular_solver metric: flops = total_ops<T>(m n k / 2, m n k / 2), k = order of A
 (miniapp/miniapp_triangular_solver.cpp:143-144, :170); device-resident operands, CUDA events around the solve.
 
-  python profiles/tools/bench_trsolve.py [type side uplo op m n nb] ...
+  python profiles/tools/bench_trsolve.py [--both] [type side uplo op m n nb] ...
+  --both: every case with DLAFB_TRSOLVE_LOOKAHEAD=0 and =1 (the variable is read when the plan is created)
   default: d L L N 16384 16384 512, d R L C 16384 16384 512, d L L C 16384 16384 512, d L L N 32768 4096 512,
-           z L L N 8192 8192 512, s L L N 16384 16384 512
+           z L L N 8192 8192 512, s L L N 16384 16384 512, d L L N 32768 32768 512
 
 The residual max|op(A) X - alpha B| / (max|A| max|X| k eps) is formed with torch.matmul as the checker only.
 """
@@ -66,14 +67,22 @@ def main():
     L = pkg.lib()
     torch.cuda.set_device(0)
     args = sys.argv[1:]
+    both = "--both" in args
+    args = [a for a in args if a != "--both"]
     cases = [(args[i], args[i + 1], args[i + 2], args[i + 3], int(args[i + 4]), int(args[i + 5]), int(args[i + 6]))
              for i in range(0, len(args), 7)] or \
         [("d", "L", "L", "N", 16384, 16384, 512), ("d", "R", "L", "C", 16384, 16384, 512),
          ("d", "L", "L", "C", 16384, 16384, 512), ("d", "L", "L", "N", 32768, 4096, 512),
-         ("z", "L", "L", "N", 8192, 8192, 512), ("s", "L", "L", "N", 16384, 16384, 512)]
+         ("z", "L", "L", "N", 8192, 8192, 512), ("s", "L", "L", "N", 16384, 16384, 512),
+         ("d", "L", "L", "N", 32768, 32768, 512)]
     for c in cases:
-        print(json.dumps(run(pkg, L, *c)), flush=True)
-        torch.cuda.empty_cache()
+        for la in (("0", "1") if both else (os.environ.get("DLAFB_TRSOLVE_LOOKAHEAD"),)):
+            if la is not None:
+                os.environ["DLAFB_TRSOLVE_LOOKAHEAD"] = la
+            r = run(pkg, L, *c)
+            r["lookahead"] = la if la is not None else "default"
+            print(json.dumps(r), flush=True)
+            torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

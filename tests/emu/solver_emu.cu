@@ -7,10 +7,14 @@
 // What this pins without a GPU: the reduction of the 24 side/uplo/op/diag cases to the two canonical solves, every
 // pointer offset and leading dimension handed to the kernels, the tile-inverse recurrence (lower/upper/unit), the
 // workspace sizes (workspaces are NaN-filled, so reading anything the algorithm did not write poisons the result),
-// and that no contraction is asked to run with C aliasing an operand.
+// that no contraction is asked to run with C aliasing an operand, and - for the two-stream look-ahead variant - that
+// the events order every pair of operations with overlapping operands (replay under adversarial interleavings plus
+// a happens-before check).
 #include <cmath>
 #include <cstring>
+#include <functional>
 #include <limits>
+#include <utility>
 #include <vector>
 
 #include "triangular_solver.h"
@@ -44,79 +48,277 @@ bool overlap(const T* a, long long lda, int ra, int ca, const T* b, long long ld
   return false;
 }
 
+// One operand: the elements {p + (i + j*ld) * es : i < rows, j < cols}, in bytes.
+struct Rect {
+  const char* p;
+  long long ld;
+  int rows, cols;
+  size_t es;
+};
+
+inline bool rects_overlap(const Rect& a, const Rect& b) {
+  if (a.rows <= 0 || a.cols <= 0 || b.rows <= 0 || b.cols <= 0)
+    return false;
+  const char* a_end = a.p + ((long long)(a.cols - 1) * a.ld + a.rows) * (long long)a.es;
+  const char* b_end = b.p + ((long long)(b.cols - 1) * b.ld + b.rows) * (long long)b.es;
+  if (a_end <= b.p || b_end <= a.p)
+    return false;
+  for (int j = 0; j < a.cols; ++j) {
+    const char* a0 = a.p + (long long)j * a.ld * (long long)a.es;
+    const char* a1 = a0 + (long long)a.rows * (long long)a.es;
+    for (int l = 0; l < b.cols; ++l) {
+      const char* b0 = b.p + (long long)l * b.ld * (long long)b.es;
+      const char* b1 = b0 + (long long)b.rows * (long long)b.es;
+      if (a0 < b1 && b0 < a1)
+        return true;
+    }
+  }
+  return false;
+}
+
+// Executor on the host. Immediate mode: every operation runs when it is issued (one lane). Deferred mode: the
+// operations are queued per lane, signal / wait become markers, and drain() replays the two queues preferring one
+// lane whenever the events allow it (the other lane then runs as late as possible) while tracking, per operation,
+// what it is ordered after on the other lane. races() then looks at every pair of operations the events leave
+// unordered and reports overlapping write/write or read/write operands.
 template <class T>
 struct HostOps {
   using R = typename Tr<T>::Real;
+  struct Op {
+    int kind = 0;  // 0 operation, 1 signal, 2 wait
+    int ev = 0, gen = 0;
+    std::function<int()> fn;
+    std::vector<Rect> reads, writes;
+    int own = 0, known = 0;  // filled by drain(): index on its lane, highest index of the other lane ordered before it
+  };
+  bool deferred = false;
+  int cur = 0;
   int hazards = 0;
+  std::vector<Op> q[2];
+  int sig_enq[kTriSolveEvents] = {};
+
+  template <class P>
+  static Rect rect(const P* p, long long ld, int rows, int cols) {
+    return Rect{reinterpret_cast<const char*>(p), ld, rows, cols, sizeof(P)};
+  }
+  int issue(Op&& op) {
+    if (!deferred)
+      return op.fn();
+    q[cur].push_back(std::move(op));
+    return 0;
+  }
+  void lane(int l) { cur = l; }
+  int signal(int ev) {
+    if (!deferred)
+      return 0;
+    Op op;
+    op.kind = 1;
+    op.ev = ev;
+    op.gen = ++sig_enq[ev];
+    q[cur].push_back(std::move(op));
+    return 0;
+  }
+  int wait(int ev) {
+    if (!deferred)
+      return 0;
+    Op op;
+    op.kind = 2;
+    op.ev = ev;
+    op.gen = sig_enq[ev];
+    q[cur].push_back(std::move(op));
+    return 0;
+  }
+
+  // Replays the queues; `prefer` = the lane that runs whenever it can. Returns the first error (9100: deadlock).
+  int drain(int prefer) {
+    size_t head[2] = {0, 0};
+    int own[2] = {0, 0}, known[2] = {0, 0};
+    int sig_done[kTriSolveEvents] = {};
+    std::vector<std::pair<int, int>> sig_at[kTriSolveEvents];  // per generation: (lane, ops executed on it so far)
+    for (auto& v : sig_at)
+      v.push_back({0, 0});
+    int first_error = 0;
+    while (head[0] < q[0].size() || head[1] < q[1].size()) {
+      bool progressed = false;
+      for (int pass = 0; pass < 2 && !progressed; ++pass) {
+        const int l = pass == 0 ? prefer : 1 - prefer;
+        if (head[l] >= q[l].size())
+          continue;
+        Op& op = q[l][head[l]];
+        if (op.kind == 2 && sig_done[op.ev] < op.gen)
+          continue;  // blocked
+        if (op.kind == 0) {
+          op.own = ++own[l];
+          op.known = known[l];
+          const int e = op.fn();
+          if (e != 0 && first_error == 0)
+            first_error = e;
+        }
+        else if (op.kind == 1) {
+          sig_done[op.ev] = op.gen;
+          sig_at[op.ev].push_back({l, own[l]});
+        }
+        else if (op.gen > 0) {
+          const auto& at = sig_at[op.ev][op.gen];
+          if (at.first != l && at.second > known[l])
+            known[l] = at.second;
+        }
+        ++head[l];
+        progressed = true;
+      }
+      if (!progressed)
+        return 9100;
+    }
+    return first_error;
+  }
+
+  int races() const {
+    int n = 0;
+    for (const Op& a : q[0]) {
+      if (a.kind != 0)
+        continue;
+      for (const Op& b : q[1]) {
+        if (b.kind != 0)
+          continue;
+        if (b.known >= a.own || a.known >= b.own)
+          continue;  // ordered by an event
+        bool clash = false;
+        for (const Rect& wa : a.writes) {
+          for (const Rect& wb : b.writes)
+            clash = clash || rects_overlap(wa, wb);
+          for (const Rect& rb : b.reads)
+            clash = clash || rects_overlap(wa, rb);
+        }
+        for (const Rect& wb : b.writes)
+          for (const Rect& ra : a.reads)
+            clash = clash || rects_overlap(wb, ra);
+        n += clash;
+      }
+    }
+    return n;
+  }
+
   int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
               long long ldc) {
     if (M <= 0 || N <= 0)
       return 0;
-    if (overlap<T>(C, ldc, M, N, A, lda, M, K) || overlap<T>(C, ldc, M, N, B, ldb, N, K)) {
-      ++hazards;
-      return 9001;
-    }
-    for (int j = 0; j < N; ++j)
-      for (int i = 0; i < M; ++i) {
-        T acc = Tr<T>::zero();
-        for (int k = 0; k < K; ++k)
-          acc = Tr<T>::fma(A[i + k * lda], Tr<T>::conj(B[j + k * ldb]), acc);
-        T v = Tr<T>::scale(acc, alpha);
-        if (beta != R(0))
-          v = Tr<T>::add(v, Tr<T>::scale(C[i + j * ldc], beta));
-        C[i + j * ldc] = v;
+    Op op;
+    op.reads = {rect(A, lda, M, K), rect(B, ldb, N, K)};
+    if (beta != R(0))
+      op.reads.push_back(rect(C, ldc, M, N));
+    op.writes = {rect(C, ldc, M, N)};
+    op.fn = [=]() -> int {
+      if (overlap<T>(C, ldc, M, N, A, lda, M, K) || overlap<T>(C, ldc, M, N, B, ldb, N, K)) {
+        ++this->hazards;
+        return 9001;
       }
-    return 0;
+      for (int j = 0; j < N; ++j)
+        for (int i = 0; i < M; ++i) {
+          T acc = Tr<T>::zero();
+          for (int k = 0; k < K; ++k)
+            acc = Tr<T>::fma(A[i + k * lda], Tr<T>::conj(B[j + k * ldb]), acc);
+          T v = Tr<T>::scale(acc, alpha);
+          if (beta != R(0))
+            v = Tr<T>::add(v, Tr<T>::scale(C[i + j * ldc], beta));
+          C[i + j * ldc] = v;
+        }
+      return 0;
+    };
+    return issue(std::move(op));
   }
   // aux.cu transpose_kernel: out(j, i) = op(in(i, j)); tri 'L' writes only out rows >= out cols, 'U' rows <= cols
   int transpose(int m, int n, const T* in, long long ldin, T* out, long long ldout, int conj, char tri) {
-    if (overlap<T>(out, ldout, n, m, in, ldin, m, n)) {
-      ++hazards;
-      return 9002;
-    }
-    for (int i = 0; i < m; ++i)
-      for (int j = 0; j < n; ++j) {
-        if ((tri == 'L' && j < i) || (tri == 'U' && j > i))
-          continue;
-        const T v = in[i + j * ldin];
-        out[j + i * ldout] = conj ? Tr<T>::conj(v) : v;
+    if (m <= 0 || n <= 0)
+      return 0;
+    Op op;
+    op.reads = {rect(in, ldin, m, n)};
+    op.writes = {rect(out, ldout, n, m)};
+    op.fn = [=]() -> int {
+      if (overlap<T>(out, ldout, n, m, in, ldin, m, n)) {
+        ++this->hazards;
+        return 9002;
       }
-    return 0;
+      for (int i = 0; i < m; ++i)
+        for (int j = 0; j < n; ++j) {
+          if ((tri == 'L' && j < i) || (tri == 'U' && j > i))
+            continue;
+          const T v = in[i + j * ldin];
+          out[j + i * ldout] = conj ? Tr<T>::conj(v) : v;
+        }
+      return 0;
+    };
+    return issue(std::move(op));
   }
   int lacpy(int m, int n, const T* a, long long lda, T* b, long long ldb) {
-    for (int j = 0; j < n; ++j)
-      for (int i = 0; i < m; ++i)
-        b[i + j * ldb] = a[i + j * lda];
-    return 0;
+    if (m <= 0 || n <= 0)
+      return 0;
+    Op op;
+    op.reads = {rect(a, lda, m, n)};
+    op.writes = {rect(b, ldb, m, n)};
+    op.fn = [=]() -> int {
+      for (int j = 0; j < n; ++j)
+        for (int i = 0; i < m; ++i)
+          b[i + j * ldb] = a[i + j * lda];
+      return 0;
+    };
+    return issue(std::move(op));
   }
   int tri_inverse(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w) {
-    TriInvParams p{n, nb, ldt, upper, unit};
-    const int blocks = tri_inverse_blocks(n, nb);
-    for (int b = 0; b < blocks; ++b)
-      for (int th = 0; th < kTriInvThreads; ++th)
-        tri_inverse_body<T>(p, t, w, b, th, kTriInvThreads);
-    return 0;
+    Op op;
+    op.reads = {rect(t, ldt, n, n)};
+    op.writes = {rect(w, 1, tri_inverse_blocks(n, nb) * nb * nb, 1)};
+    op.fn = [=]() -> int {
+      TriInvParams p{n, nb, ldt, upper, unit};
+      const int blocks = tri_inverse_blocks(n, nb);
+      for (int b = 0; b < blocks; ++b)
+        for (int th = 0; th < kTriInvThreads; ++th)
+          tri_inverse_body<T>(p, t, w, b, th, kTriInvThreads);
+      return 0;
+    };
+    return issue(std::move(op));
   }
   int scale(int m, int n, T* b, long long ldb, T alpha, int conj) {
-    for (int by = 0; by < scale_blocks_y(n); ++by)
-      for (int bx = 0; bx < scale_blocks_x(m); ++bx)
-        for (int th = 0; th < kScaleRows; ++th)
-          scale_body<T>(m, n, b, ldb, alpha, conj, bx, by, th);
-    return 0;
+    if (m <= 0 || n <= 0)
+      return 0;
+    Op op;
+    op.reads = {rect(b, ldb, m, n)};
+    op.writes = {rect(b, ldb, m, n)};
+    op.fn = [=]() -> int {
+      for (int by = 0; by < scale_blocks_y(n); ++by)
+        for (int bx = 0; bx < scale_blocks_x(m); ++bx)
+          for (int th = 0; th < kScaleRows; ++th)
+            scale_body<T>(m, n, b, ldb, alpha, conj, bx, by, th);
+      return 0;
+    };
+    return issue(std::move(op));
   }
 };
 
+// lookahead = 0: one lane, immediate. lookahead = 1: the two-lane variant, replayed with lane `prefer` running
+// whenever it can; *races = number of unordered operation pairs with overlapping operands.
 template <class T>
 int solve(char side, char uplo, char op, char diag, int m, int n, int nb, const void* alpha, const void* a,
-          long long lda, void* b, long long ldb) {
+          long long lda, void* b, long long ldb, int lookahead = 0, int prefer = 0, int* races = nullptr) {
   TriSolveDesc d{side, uplo, op, diag, m, n, nb};
   std::vector<T> tcopy(tri_solve_tcopy_elems(d), nan_value<T>());
   std::vector<T> winv(tri_solve_winv_elems(d), nan_value<T>());
-  std::vector<T> panel(tri_solve_panel_elems(d), nan_value<T>());
+  std::vector<T> panel(tri_solve_panel_elems(d) * (lookahead ? 2 : 1), nan_value<T>());
   TriSolveWork<T> w{tcopy.data(), tri_solve_ldt(d), winv.data(), panel.data(), tri_solve_ldp(d)};
   HostOps<T> ops;
-  return triangular_solve<T>(ops, d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda, static_cast<T*>(b),
-                             ldb, w);
+  if (lookahead) {
+    w.lookahead = 1;
+    w.panel_stride = tri_solve_panel_elems(d);
+    ops.deferred = true;
+  }
+  int e = triangular_solve<T>(ops, d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda, static_cast<T*>(b),
+                              ldb, w);
+  if (lookahead) {
+    if (e == 0)
+      e = ops.drain(prefer);
+    if (races)
+      *races = ops.races();
+  }
+  return e;
 }
 
 template <class T>
@@ -131,6 +333,11 @@ int inverse(int upper, int unit, int n, int nb, const void* t, long long ldt, vo
   int emu_triangular_solver_##X(char side, char uplo, char op, char diag, int m, int n, int nb, const void* alpha, \
                                 const void* a, long long lda, void* b, long long ldb) {                             \
     return solve<T>(side, uplo, op, diag, m, n, nb, alpha, a, lda, b, ldb);                                         \
+  }                                                                                                                 \
+  int emu_triangular_solver_la_##X(char side, char uplo, char op, char diag, int m, int n, int nb,                  \
+                                   const void* alpha, const void* a, long long lda, void* b, long long ldb,        \
+                                   int prefer, int* races) {                                                        \
+    return solve<T>(side, uplo, op, diag, m, n, nb, alpha, a, lda, b, ldb, 1, prefer, races);                       \
   }                                                                                                                 \
   int emu_tri_inverse_##X(int upper, int unit, int n, int nb, const void* t, long long ldt, void* w) {              \
     return inverse<T>(upper, unit, n, nb, t, ldt, w);                                                               \
