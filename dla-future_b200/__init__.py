@@ -1,5 +1,5 @@
 """ctypes binding of libdlaf_b200.so (the C ABI in include/dlafb_kernels.h, include/dlafb_engine.h,
-include/dlafb_solver.h and include/dlaf_c/*.h). Used by tests/ and bench.py; the product itself is the shared library.
+include/dlafb_solver.h, include/dlafb_gen_to_std.h and include/dlaf_c/*.h). Used by tests/ and bench.py; the product itself is the shared library.
 
 The directory name contains a hyphen, so import it with `load_package()` from tests/conftest.py /
 bench.py (importlib), under the module name `dlaf_b200`.
@@ -84,7 +84,7 @@ def lib():
 
 
 from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
-from ._engine_api import CholeskyPlan, Grid, StepInfo, TriangularSolverPlan, schedule_step  # noqa: E402,F401
+from ._engine_api import CholeskyPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverPlan, schedule_step  # noqa: E402,F401
 
 
 def check(err, what=""):

@@ -1,5 +1,6 @@
-"""ctypes signatures of include/dlafb_engine.h and include/dlafb_solver.h plus thin Python wrappers (Grid,
-CholeskyPlan, TriangularSolverPlan) used by the tests and by bench.py. No arithmetic happens here."""
+"""ctypes signatures of include/dlafb_engine.h, include/dlafb_solver.h and include/dlafb_gen_to_std.h plus thin Python
+wrappers (Grid, CholeskyPlan, TriangularSolverPlan, GenToStdPlan) used by the tests and by bench.py. No arithmetic
+happens here."""
 import ctypes
 
 c_i64 = ctypes.c_int64
@@ -52,6 +53,11 @@ ENGINE_API = {
     "dlafb_triangular_solver_plan_run": (c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_triangular_solver_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
     "dlafb_triangular_solver_plan_destroy": (c_int, [c_vp]),
+    # include/dlafb_gen_to_std.h
+    "dlafb_gen_to_std_plan_create": (c_int, [ctypes.POINTER(c_vp), c_char, c_char, c_i64, c_i64]),
+    "dlafb_gen_to_std_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
+    "dlafb_gen_to_std_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
+    "dlafb_gen_to_std_plan_destroy": (c_int, [c_vp]),
 }
 
 
@@ -188,4 +194,25 @@ class TriangularSolverPlan:
     def close(self):
         if self.h:
             self.L.dlafb_triangular_solver_plan_destroy(self.h)
+            self.h = c_vp()
+
+
+class GenToStdPlan:
+    """generalized_to_standard on one GPU (include/dlafb_gen_to_std.h): A <- inv(L) A inv(L)^H / inv(U)^H A inv(U)."""
+
+    def __init__(self, L, type_, uplo, n, nb):
+        self.L = L
+        self.h = c_vp()
+        _ck(L.dlafb_gen_to_std_plan_create(ctypes.byref(self.h), type_.encode(), uplo.encode(), n, nb),
+            "gen_to_std_plan_create")
+
+    def run(self, a_ptr, lda, f_ptr, ldf, stream):
+        _ck(self.L.dlafb_gen_to_std_plan_run(self.h, a_ptr, lda, f_ptr, ldf, stream), "gen_to_std_plan_run")
+
+    def workspace_bytes(self):
+        return self.L.dlafb_gen_to_std_plan_workspace_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.dlafb_gen_to_std_plan_destroy(self.h)
             self.h = c_vp()

@@ -1,0 +1,136 @@
+// Device executor and C ABI of the generalized-to-standard reduction on one GPU (algorithm: gen_to_std.h).
+#include "gen_to_std.h"
+
+#include <cuda_runtime.h>
+
+#include <new>
+
+#include "dlafb_gen_to_std.h"
+#include "tile_ops.cuh"
+
+namespace dlafb {
+namespace {
+
+// Every operation goes to the caller's stream in program order.
+template <class T>
+struct G2sDeviceOps {
+  cudaStream_t s;
+  using R = typename Tr<T>::Real;
+  int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
+              long long ldc, int lower) {
+    return (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower);
+  }
+  int transpose(int m, int n, const T* in, long long ldin, T* out, long long ldout, int conj, char tri) {
+    return (int)dlafb::transpose<T>(s, m, n, in, ldin, out, ldout, conj, tri);
+  }
+  int lacpy(char uplo, int m, int n, const T* a, long long lda, T* b, long long ldb) {
+    return (int)dlafb::lacpy<T>(s, uplo, m, n, a, lda, b, ldb);
+  }
+  int tri_inverse(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w) {
+    TriInvParams p{n, nb, ldt, upper, unit};
+    return (int)launch_tri_inverse<T>(s, p, t, w);
+  }
+};
+
+struct G2sPlan {
+  char type, uplo;
+  int n, nb;
+  size_t elem;
+  void* base = nullptr;  // one allocation, parts at 256-byte aligned offsets
+  size_t off_winv = 0, off_akk = 0, off_tmp = 0, off_pa = 0, off_pb = 0, off_acopy = 0, off_lcopy = 0;
+  size_t bytes = 0;
+  ~G2sPlan() { cudaFree(base); }
+};
+
+size_t align_up(size_t x) { return (x + 255) & ~size_t(255); }
+
+template <class T>
+int g2s_run_typed(G2sPlan& p, void* a, long long lda, const void* f, long long ldf, cudaStream_t s) {
+  char* b = static_cast<char*>(p.base);
+  GenToStdWork<T> w{};
+  w.winv = reinterpret_cast<T*>(b + p.off_winv);
+  w.akk = reinterpret_cast<T*>(b + p.off_akk);
+  w.tmp = reinterpret_cast<T*>(b + p.off_tmp);
+  w.ldk = g2s_even(p.nb);
+  w.pa = reinterpret_cast<T*>(b + p.off_pa);
+  w.pb = reinterpret_cast<T*>(b + p.off_pb);
+  w.ldp = g2s_ldp(p.n);
+  w.acopy = reinterpret_cast<T*>(b + p.off_acopy);
+  w.lcopy = reinterpret_cast<T*>(b + p.off_lcopy);
+  w.ldc = g2s_ldp(p.n);
+  G2sDeviceOps<T> ops{s};
+  return gen_to_std<T>(ops, p.uplo, p.n, p.nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+}
+
+}  // namespace
+}  // namespace dlafb
+
+using namespace dlafb;
+
+extern "C" {
+
+int dlafb_gen_to_std_plan_create(dlafb_gen_to_std_plan_t* out, char type, char uplo, int64_t n, int64_t nb) {
+  if (!out || (type != 's' && type != 'd' && type != 'c' && type != 'z') || (uplo != 'L' && uplo != 'U') || n < 0 ||
+      nb < 1 || n > (1LL << 30) || nb > (1 << 14))
+    return -1;
+  G2sPlan* p = new (std::nothrow) G2sPlan;
+  if (!p)
+    return (int)cudaErrorMemoryAllocation;
+  p->type = type;
+  p->uplo = uplo;
+  p->n = (int)n;
+  p->nb = (int)nb;
+  p->elem = type == 's' ? 4 : type == 'z' ? 16 : 8;
+  if (n > 0) {
+    size_t off = 0;
+    auto part = [&](size_t elems) {
+      const size_t at = off;
+      off = align_up(off + elems * p->elem);
+      return at;
+    };
+    p->off_winv = part(g2s_winv_elems(p->n, p->nb));
+    p->off_akk = part(g2s_tile_elems(p->nb));
+    p->off_tmp = part(g2s_tile_elems(p->nb));
+    p->off_pa = part(g2s_panel_elems(p->n, p->nb));
+    p->off_pb = part(g2s_panel_elems(p->n, p->nb));
+    p->off_acopy = part(g2s_copy_elems(p->n, uplo));
+    p->off_lcopy = part(g2s_copy_elems(p->n, uplo));
+    p->bytes = off;
+    const cudaError_t e = cudaMalloc(&p->base, p->bytes);
+    if (e != cudaSuccess) {
+      delete p;
+      return (int)e;
+    }
+  }
+  *out = reinterpret_cast<dlafb_gen_to_std_plan_t>(p);
+  return 0;
+}
+
+int dlafb_gen_to_std_plan_run(dlafb_gen_to_std_plan_t plan, void* a, int64_t lda, const void* factor, int64_t ldf,
+                              void* stream) {
+  G2sPlan* p = reinterpret_cast<G2sPlan*>(plan);
+  if (!p)
+    return -1;
+  if (p->n == 0)
+    return 0;
+  if (!a || !factor || lda < p->n || ldf < p->n)
+    return -1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->type) {
+    case 's': return g2s_run_typed<float>(*p, a, lda, factor, ldf, s);
+    case 'd': return g2s_run_typed<double>(*p, a, lda, factor, ldf, s);
+    case 'c': return g2s_run_typed<float2>(*p, a, lda, factor, ldf, s);
+    default: return g2s_run_typed<double2>(*p, a, lda, factor, ldf, s);
+  }
+}
+
+size_t dlafb_gen_to_std_plan_workspace_bytes(dlafb_gen_to_std_plan_t plan) {
+  return plan ? reinterpret_cast<G2sPlan*>(plan)->bytes : 0;
+}
+
+int dlafb_gen_to_std_plan_destroy(dlafb_gen_to_std_plan_t plan) {
+  delete reinterpret_cast<G2sPlan*>(plan);
+  return 0;
+}
+
+}  // extern "C"

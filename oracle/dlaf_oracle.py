@@ -550,3 +550,101 @@ def triangular_solver_local(side, uplo, op, diag, alpha, a, b, mb, nb):
                     akj = ta(k, j) if op == "N" else _opm(ta(j, k), op)
                     tb(i, j)[...] += beta * (tb(i, k) @ akj)
     return b
+
+
+# ----------------------------------------------------------------------------------------------
+# Reduction of the generalized Hermitian problem to standard form (local):
+#   include/dlaf/eigensolver/gen_to_std.h:23-77 (front end), gen_to_std/impl.h:222-283 (call_L), :508-569 (call_U)
+#   analytical test: test/unit/eigensolver/test_gen_to_std.cpp:53-83,
+#                    test/include/dlaf_test/matrix/util_generic_lapack.h:70-149 (getGenToStdElementSetters)
+# ----------------------------------------------------------------------------------------------
+GEN_TO_STD_TEST_SIZES = [(0, 2), (5, 8), (34, 34), (4, 3), (16, 10), (34, 13), (32, 5)]  # test_gen_to_std.cpp:53-57
+
+
+def gen_to_std_setters(n, uplo, dtype, alpha=-2.0, beta=1.5, gamma=0.95):
+    """getGenToStdElementSetters with itype = 1: returns (T, A, RES); T is the Cholesky factor, A the Hermitian
+    matrix, RES = inv(T) A inv(T)^H (uplo 'L') or inv(T)^H A inv(T) (uplo 'U'); the triangle that is not referenced
+    holds -9.9 in all three."""
+    dtype = np.dtype(dtype)
+    i = np.arange(n, dtype=np.float64)[:, None]
+    j = np.arange(n, dtype=np.float64)[None, :]
+    t = _polar(beta / np.exp2(np.abs(i - j)), alpha * (i - j), dtype)
+    a = _polar((i + 1) * (j + 1) * (beta * beta * gamma) / np.exp2(i + j), alpha * (i - j), dtype)
+    r = _polar(gamma / np.exp2(i + j), alpha * (i - j), dtype)
+    unref = (i < j) if uplo == "L" else (i > j)
+    out = []
+    for x in (t, a, r):
+        out.append(np.asfortranarray(np.where(unref, dtype.type(-9.9), x).astype(dtype)))
+    return tuple(out)
+
+
+def _herm_from(uplo, a):
+    """Full Hermitian tile from its referenced triangle (what hemm / hegst read)."""
+    tri = np.tril(a) if uplo == "L" else np.triu(a)
+    full = tri + tri.conj().T
+    full[np.diag_indices_from(full)] = np.diag(a).real if a.dtype.kind == "c" else np.diag(a)
+    return full
+
+
+def _tile_hegst(uplo, a, b):
+    """tile::hegst(itype = 1, uplo, a, b) (lapack/tile.h:253-263 CPU, :550-575 GPU): LAPACK ?sygst / ?hegst."""
+    pre = {np.float32: "s", np.float64: "d", np.complex64: "c", np.complex128: "z"}[a.dtype.type]
+    fn = getattr(slapack, pre + ("hegst" if pre in "cz" else "sygst"))
+    res, info = fn(a, b, itype=1, lower=int(uplo == "L"))
+    assert info == 0
+    keep = np.tril(np.ones(a.shape, bool)) if uplo == "L" else np.triu(np.ones(a.shape, bool))
+    a[keep] = res[keep]
+
+
+def _tile_her2k(uplo, x, y, c):
+    """c (uplo triangle) <- c - x y^H - y x^H."""
+    upd = c - x @ y.conj().T - y @ x.conj().T
+    keep = np.tril(np.ones(c.shape, bool)) if uplo == "L" else np.triu(np.ones(c.shape, bool))
+    c[keep] = upd[keep]
+
+
+def gen_to_std_local(uplo, a, t, nb):
+    """In-place tile loops of GenToStd::call_L / call_U (local). `a` holds the Hermitian matrix in its uplo triangle,
+    `t` the Cholesky factor; only the uplo triangles are referenced, only the uplo triangle of `a` is written."""
+    n = a.shape[0]
+    nt = -(-n // nb) if n else 0
+    ta = lambda i, j: a[i * nb:(i + 1) * nb, j * nb:(j + 1) * nb]
+    tt = lambda i, j: t[i * nb:(i + 1) * nb, j * nb:(j + 1) * nb]
+    half = a.dtype.type(0.5)
+    for k in range(nt):
+        _tile_hegst(uplo, ta(k, k), tt(k, k))
+        if k == nt - 1:
+            continue
+        akk = _herm_from(uplo, ta(k, k))
+        if uplo == "L":
+            for i in range(k + 1, nt):
+                _tile_trsm("R", "L", "C", "N", 1, tt(k, k), ta(i, k))
+                ta(i, k)[...] -= half * (tt(i, k) @ akk)
+            for j in range(k + 1, nt):
+                _tile_her2k("L", ta(j, k), tt(j, k), ta(j, j))
+                for i in range(j + 1, nt):
+                    ta(i, j)[...] -= ta(i, k) @ tt(j, k).conj().T
+                    ta(i, j)[...] -= tt(i, k) @ ta(j, k).conj().T
+            for i in range(k + 1, nt):
+                ta(i, k)[...] -= half * (tt(i, k) @ akk)
+            for j in range(k + 1, nt):
+                _tile_trsm("L", "L", "N", "N", 1, tt(j, j), ta(j, k))
+                for i in range(j + 1, nt):
+                    ta(i, k)[...] -= tt(i, j) @ ta(j, k)
+        else:
+            for i in range(k + 1, nt):
+                _tile_trsm("L", "U", "C", "N", 1, tt(k, k), ta(k, i))
+                ta(k, i)[...] -= half * (akk @ tt(k, i))
+            for i in range(k + 1, nt):
+                # her2k(Upper, ConjTrans): c <- c - x^H y - y^H x
+                _tile_her2k("U", ta(k, i).conj().T, tt(k, i).conj().T, ta(i, i))
+                for j in range(i + 1, nt):
+                    ta(i, j)[...] -= ta(k, i).conj().T @ tt(k, j)
+                    ta(i, j)[...] -= tt(k, i).conj().T @ ta(k, j)
+            for i in range(k + 1, nt):
+                ta(k, i)[...] -= half * (akk @ tt(k, i))
+            for i in range(k + 1, nt):
+                _tile_trsm("R", "U", "N", "N", 1, tt(i, i), ta(k, i))
+                for j in range(i + 1, nt):
+                    ta(k, j)[...] -= ta(k, i) @ tt(i, j)
+    return a

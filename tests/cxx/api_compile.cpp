@@ -1,0 +1,28 @@
+// TEST INFRASTRUCTURE: instantiates every public C++ front end of include/dlaf/ for the four element types, so that
+// the CPU test-suite (tests/test_cxx_headers.py) catches a header that no longer compiles. Never run.
+#include "dlaf/eigensolver/gen_to_std.h"
+#include "dlaf/factorization/cholesky.h"
+#include "dlaf/solver/triangular.h"
+
+#include <complex>
+
+template <class T>
+void instantiate(dlaf::comm::CommunicatorGrid& grid) {
+  using namespace dlaf;
+  Matrix<T, Device::GPU> a(LocalElementSize(8, 8), TileElementSize(4, 4));
+  Matrix<T, Device::GPU> b(LocalElementSize(8, 8), TileElementSize(4, 4));
+  cholesky_factorization<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, a);
+  cholesky_factorization<Backend::GPU, Device::GPU, T>(grid, blas::Uplo::Lower, a);
+  triangular_solver<Backend::GPU, Device::GPU, T>(blas::Side::Left, blas::Uplo::Lower, blas::Op::NoTrans,
+                                                  blas::Diag::NonUnit, T(1), a, b);
+  eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, b, a);
+  a.waitLocalTiles();
+  b.waitLocalTiles();
+}
+
+void instantiate_all(dlaf::comm::CommunicatorGrid& grid) {
+  instantiate<float>(grid);
+  instantiate<double>(grid);
+  instantiate<std::complex<float>>(grid);
+  instantiate<std::complex<double>>(grid);
+}

@@ -17,6 +17,7 @@
 #include <utility>
 #include <vector>
 
+#include "gen_to_std.h"
 #include "triangular_solver.h"
 
 namespace {
@@ -198,8 +199,9 @@ struct HostOps {
     return n;
   }
 
+  // lower != 0: only the elements with row >= col are touched (gemm_dmma.cu / gemm_simt.cu RECT mode)
   int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
-              long long ldc) {
+              long long ldc, int lower = 0) {
     if (M <= 0 || N <= 0)
       return 0;
     Op op;
@@ -213,7 +215,7 @@ struct HostOps {
         return 9001;
       }
       for (int j = 0; j < N; ++j)
-        for (int i = 0; i < M; ++i) {
+        for (int i = lower ? j : 0; i < M; ++i) {
           T acc = Tr<T>::zero();
           for (int k = 0; k < K; ++k)
             acc = Tr<T>::fma(A[i + k * lda], Tr<T>::conj(B[j + k * ldb]), acc);
@@ -259,6 +261,28 @@ struct HostOps {
       for (int j = 0; j < n; ++j)
         for (int i = 0; i < m; ++i)
           b[i + j * ldb] = a[i + j * lda];
+      return 0;
+    };
+    return issue(std::move(op));
+  }
+  // aux.cu lacpy_kernel with uplo: 'L' copies rows >= cols, 'U' rows <= cols
+  int lacpy(char uplo, int m, int n, const T* a, long long lda, T* b, long long ldb) {
+    if (m <= 0 || n <= 0)
+      return 0;
+    Op op;
+    op.reads = {rect(a, lda, m, n)};
+    op.writes = {rect(b, ldb, m, n)};
+    op.fn = [=]() -> int {
+      if (overlap<T>(b, ldb, m, n, a, lda, m, n)) {
+        ++this->hazards;
+        return 9003;
+      }
+      for (int j = 0; j < n; ++j)
+        for (int i = 0; i < m; ++i) {
+          if ((uplo == 'L' && i < j) || (uplo == 'U' && i > j))
+            continue;
+          b[i + j * ldb] = a[i + j * lda];
+        }
       return 0;
     };
     return issue(std::move(op));
@@ -327,6 +351,19 @@ int inverse(int upper, int unit, int n, int nb, const void* t, long long ldt, vo
   return ops.tri_inverse(upper, unit, n, nb, static_cast<const T*>(t), ldt, static_cast<T*>(w));
 }
 
+// Generalized-to-standard reduction: the product's algorithm template over the host executor, NaN-filled workspaces.
+template <class T>
+int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {
+  std::vector<T> winv(g2s_winv_elems(n, nb), nan_value<T>());
+  std::vector<T> akk(g2s_tile_elems(nb), nan_value<T>()), tmp(g2s_tile_elems(nb), nan_value<T>());
+  std::vector<T> pa(g2s_panel_elems(n, nb), nan_value<T>()), pb(g2s_panel_elems(n, nb), nan_value<T>());
+  std::vector<T> ac(g2s_copy_elems(n, uplo), nan_value<T>()), lc(g2s_copy_elems(n, uplo), nan_value<T>());
+  GenToStdWork<T> w{winv.data(), akk.data(), tmp.data(), g2s_even(nb), pa.data(), pb.data(), g2s_ldp(n),
+                    ac.data(), lc.data(), g2s_ldp(n)};
+  HostOps<T> ops;
+  return gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+}
+
 }  // namespace
 
 #define EMU_TYPED(X, T)                                                                                             \
@@ -341,6 +378,9 @@ int inverse(int upper, int unit, int n, int nb, const void* t, long long ldt, vo
   }                                                                                                                 \
   int emu_tri_inverse_##X(int upper, int unit, int n, int nb, const void* t, long long ldt, void* w) {              \
     return inverse<T>(upper, unit, n, nb, t, ldt, w);                                                               \
+  }                                                                                                                 \
+  int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
+    return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
   }
 
 extern "C" {

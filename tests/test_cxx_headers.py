@@ -1,0 +1,21 @@
+"""The public C++ front ends (include/dlaf/**: cholesky_factorization, triangular_solver, generalized_to_standard,
+Matrix, Distribution, CommunicatorGrid) must compile and instantiate for the four element types with the host
+compiler alone (they are header-only wrappers over the C ABI). Syntax check only: nothing is run."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_front_ends_instantiate_for_all_types():
+    cuda_inc = "/usr/local/cuda/include"
+    if shutil.which("g++") is None or not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("needs g++ and the CUDA headers")
+    cmd = ["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "include", "dlafb_mpi_shim"), "-I" + cuda_inc,
+           os.path.join(ROOT, "tests", "cxx", "api_compile.cpp")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
