@@ -84,7 +84,8 @@ def lib():
 
 
 from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
-from ._engine_api import CholeskyPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverPlan, schedule_step  # noqa: E402,F401
+from ._engine_api import (CholeskyPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverDistPlan,  # noqa: E402,F401
+                          TriangularSolverPlan, schedule_step)
 
 
 def check(err, what=""):

@@ -53,6 +53,12 @@ ENGINE_API = {
     "dlafb_triangular_solver_plan_run": (c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_triangular_solver_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
     "dlafb_triangular_solver_plan_destroy": (c_int, [c_vp]),
+    "dlafb_triangular_solver_dist_plan_create": (c_int, [ctypes.POINTER(c_vp), c_vp, c_char, c_char, c_char, c_char,
+                                                         c_char, c_i64, c_i64, c_i64, c_i64, c_int, c_int]),
+    "dlafb_triangular_solver_dist_plan_local_sizes": (c_int, [c_vp, P_i64, P_i64, P_i64, P_i64]),
+    "dlafb_triangular_solver_dist_plan_run": (c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
+    "dlafb_triangular_solver_dist_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
+    "dlafb_triangular_solver_dist_plan_destroy": (c_int, [c_vp]),
     # include/dlafb_gen_to_std.h
     "dlafb_gen_to_std_plan_create": (c_int, [ctypes.POINTER(c_vp), c_char, c_char, c_i64, c_i64]),
     "dlafb_gen_to_std_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
@@ -194,6 +200,35 @@ class TriangularSolverPlan:
     def close(self):
         if self.h:
             self.L.dlafb_triangular_solver_plan_destroy(self.h)
+            self.h = c_vp()
+
+
+class TriangularSolverDistPlan:
+    """dlaf::triangular_solver(grid, ...) (include/dlafb_solver.h): collective over the grid, local blocks in and out."""
+
+    def __init__(self, L, grid, type_, side, uplo, op, diag, m, n, mb, nb, src=(0, 0)):
+        self.L = L
+        self.type = type_
+        self.h = c_vp()
+        _ck(L.dlafb_triangular_solver_dist_plan_create(ctypes.byref(self.h), grid.h, type_.encode(), side.encode(),
+                                                       uplo.encode(), op.encode(), diag.encode(), m, n, mb, nb, src[0],
+                                                       src[1]), "triangular_solver_dist_plan_create")
+        v = [c_i64() for _ in range(4)]
+        _ck(L.dlafb_triangular_solver_dist_plan_local_sizes(self.h, *v), "triangular_solver_dist_plan_local_sizes")
+        self.a_rows, self.a_cols, self.b_rows, self.b_cols = (x.value for x in v)
+
+    def run(self, alpha, a_ptr, lda, b_ptr, ldb, stream):
+        al = complex(alpha)
+        buf = _CTYPE[self.type](al.real, al.imag) if self.type in "cz" else _CTYPE[self.type](al.real)
+        _ck(self.L.dlafb_triangular_solver_dist_plan_run(self.h, ctypes.addressof(buf), a_ptr, lda, b_ptr, ldb, stream),
+            "triangular_solver_dist_plan_run")
+
+    def workspace_bytes(self):
+        return self.L.dlafb_triangular_solver_dist_plan_workspace_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.dlafb_triangular_solver_dist_plan_destroy(self.h)
             self.h = c_vp()
 
 

@@ -20,8 +20,8 @@ __global__ void __launch_bounds__(kScaleRows) scale_kernel(int m, int n, T* __re
 
 template <class T>
 cudaError_t launch_tri_inverse(cudaStream_t stream, const TriInvParams& p, const T* t, T* w) {
-  const int blocks = tri_inverse_blocks(p.n, p.nb);
-  if (blocks == 0)
+  const int blocks = p.count >= 0 ? p.count : tri_inverse_blocks(p.n, p.nb);
+  if (blocks <= 0)
     return cudaSuccess;
   tri_inverse_kernel<T><<<blocks, kTriInvThreads, 0, stream>>>(p, t, w);
   ++g_launches;

@@ -59,6 +59,14 @@ struct TriInvParams {
   long long ldt;   // leading dimension of the triangular matrix
   int upper;       // 0: lower triangular, 1: upper
   int unit;        // 1: the diagonal is not referenced and taken as 1
+  // Placement of the tiles (defaults: the diagonal tiles of one n x n matrix). CTA b inverts GLOBAL diagonal tile
+  // g0 + b*gstep (its order is min(nb, n - that*nb)), stored at tile position (row0 + b*row_step, col0 + b*col_step)
+  // of t: the diagonal tiles that one rank of a 2D block-cyclic grid owns form such a progression (gstep = lcm(P, Q),
+  // row_step = gstep / P, col_step = gstep / Q). count >= 0: number of CTAs (else ceil(n / nb)).
+  int g0 = 0, gstep = 1;
+  int row0 = 0, row_step = 1;
+  int col0 = 0, col_step = 1;
+  int count = -1;
 };
 
 // Rows of a column that one thread keeps in registers at a time (tri_inverse_body).
@@ -82,11 +90,12 @@ __host__ __device__ inline void tri_inverse_body(const TriInvParams p, const T* 
                                                  int block, int thread, int nthreads) {
   using R = typename Tr<T>::Real;
   constexpr int RC = TriInvChunk<T>::value;
-  const int k0 = block * p.nb;
+  const int k0 = (p.g0 + block * p.gstep) * p.nb;
   const int order = p.n - k0 < p.nb ? p.n - k0 : p.nb;
   if (order <= 0)
     return;
-  const T* tb = t + k0 + (long long)k0 * p.ldt;
+  const T* tb = t + (long long)(p.row0 + block * p.row_step) * p.nb +
+                (long long)(p.col0 + block * p.col_step) * p.nb * p.ldt;
   T* wb = w + (size_t)block * p.nb * p.nb;
   const int last = order - 1;
   const int upper = p.upper;

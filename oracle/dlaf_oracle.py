@@ -648,3 +648,26 @@ def gen_to_std_local(uplo, a, t, nb):
                 for j in range(i + 1, nt):
                     ta(k, j)[...] -= ta(k, i) @ tt(i, j)
     return a
+
+
+# ----------------------------------------------------------------------------------------------
+# Local blocks of a rectangular 2D block-cyclic matrix (matrix::Distribution with (mb x nb) tiles,
+# include/dlaf/matrix/distribution.h, util_distribution.h:85-175): index lists per rank.
+# ----------------------------------------------------------------------------------------------
+def local_indices(n, nb, nprocs, rank, src):
+    """Global element indices, in local order, of the part of an axis of n elements (tiles of nb) that `rank` of
+    `nprocs` owns when tile 0 belongs to `src` (rank_global_tile / global_tile_from_local_tile)."""
+    idx = []
+    nt = -(-n // nb) if n else 0
+    for g in range(nt):
+        if (g + src) % nprocs == rank:
+            idx.extend(range(g * nb, min(n, (g + 1) * nb)))
+    return np.asarray(idx, dtype=np.int64)
+
+
+def local_block(a_global, mb, nb, grid, rank, src=(0, 0)):
+    """The local block of `rank` = (pr, pc) as a Fortran-ordered copy."""
+    m, n = a_global.shape
+    ri = local_indices(m, mb, grid[0], rank[0], src[0])
+    ci = local_indices(n, nb, grid[1], rank[1], src[1])
+    return np.asfortranarray(a_global[np.ix_(ri, ci)]), ri, ci

@@ -17,8 +17,13 @@
 #include <utility>
 #include <vector>
 
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+
 #include "gen_to_std.h"
 #include "triangular_solver.h"
+#include "triangular_solver_dist.h"
 
 namespace {
 using namespace dlafb;
@@ -364,6 +369,133 @@ int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void*
   return gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
 }
 
+// ---- simulated grid: one host thread per rank, collectives through shared memory -------------------------------
+// One communicator (a grid row or a grid column): a reusable barrier and the buffer pointers its members published.
+struct SimComm {
+  std::mutex mu;
+  std::condition_variable cv;
+  int size = 1, arrived = 0;
+  unsigned long long gen = 0;
+  std::vector<void*> ptr;
+  std::vector<size_t> cnt;
+  int mismatches = 0;
+  void barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    const unsigned long long g = gen;
+    if (++arrived == size) {
+      arrived = 0;
+      ++gen;
+      cv.notify_all();
+    }
+    else {
+      cv.wait(lk, [&] { return gen != g; });
+    }
+  }
+};
+
+template <class T>
+struct DistHostOps : HostOps<T> {
+  SimComm* row = nullptr;  // members ordered by grid column
+  SimComm* col = nullptr;  // members ordered by grid row
+  int me_row = 0, me_col = 0;  // my index inside them
+  int tri_inverse_local(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w, int g0, int gstep, int row0,
+                        int row_step, int col0, int col_step, int count) {
+    TriInvParams p{n, nb, ldt, upper, unit, g0, gstep, row0, row_step, col0, col_step, count};
+    for (int b = 0; b < count; ++b)
+      for (int th = 0; th < kTriInvThreads; ++th)
+        tri_inverse_body<T>(p, t, w, b, th, kTriInvThreads);
+    return 0;
+  }
+  int zero(int m, int n, T* a, long long lda) {
+    for (int j = 0; j < n; ++j)
+      for (int i = 0; i < m; ++i)
+        a[i + j * lda] = Tr<T>::zero();
+    return 0;
+  }
+  // every member must arrive with the same count: a mismatch is what NCCL would turn into a hang or corruption
+  static int bcast(SimComm* c, int me, int root, T* p, size_t count) {
+    c->ptr[me] = p;
+    c->cnt[me] = count;
+    c->barrier();
+    int bad = 0;
+    for (int i = 0; i < c->size; ++i)
+      bad += c->cnt[i] != count;
+    if (me != root && !bad)
+      std::memcpy(p, c->ptr[root], count * sizeof(T));
+    c->barrier();
+    return bad ? 9200 : 0;
+  }
+  static int reduce(SimComm* c, int me, int root, T* p, size_t count) {
+    c->ptr[me] = p;
+    c->cnt[me] = count;
+    c->barrier();
+    int bad = 0;
+    for (int i = 0; i < c->size; ++i)
+      bad += c->cnt[i] != count;
+    if (me == root && !bad)
+      for (int i = 0; i < c->size; ++i)
+        if (i != root) {
+          const T* q = static_cast<const T*>(c->ptr[i]);
+          for (size_t x = 0; x < count; ++x)
+            p[x] = Tr<T>::add(p[x], q[x]);
+        }
+    c->barrier();
+    // NCCL leaves the non-root buffers undefined: poison them so that nothing can depend on their content
+    if (me != root && !bad)
+      for (size_t x = 0; x < count; ++x)
+        p[x] = nan_value<T>();
+    return bad ? 9201 : 0;
+  }
+  int bcast_row(int root, T* p, size_t count) { return bcast(row, me_row, root, p, count); }
+  int bcast_col(int root, T* p, size_t count) { return bcast(col, me_col, root, p, count); }
+  int reduce_row(int root, T* p, size_t count) { return reduce(row, me_row, root, p, count); }
+  int reduce_col(int root, T* p, size_t count) { return reduce(col, me_col, root, p, count); }
+};
+
+// All the ranks of a P x Q grid in one process; a[r], b[r] = local blocks of rank r = pr * Q + pc.
+template <class T>
+int solve_dist(int P, int Q, int src_r, int src_c, char side, char uplo, char op, char diag, int m, int n, int mb, int nb,
+               const void* alpha, void* const* a, const long long* lda, void* const* b, const long long* ldb) {
+  std::vector<SimComm> rows(P), cols(Q);
+  for (auto& c : rows) {
+    c.size = Q;
+    c.ptr.assign(Q, nullptr);
+    c.cnt.assign(Q, 0);
+  }
+  for (auto& c : cols) {
+    c.size = P;
+    c.ptr.assign(P, nullptr);
+    c.cnt.assign(P, 0);
+  }
+  std::vector<int> err(P * Q, 0);
+  std::vector<std::thread> th;
+  for (int pr = 0; pr < P; ++pr)
+    for (int pc = 0; pc < Q; ++pc)
+      th.emplace_back([&, pr, pc] {
+        const int r = pr * Q + pc;
+        TriDistDesc d{side, uplo, op, diag, m, n, mb, nb, P, Q, pr, pc, src_r, src_c};
+        const TriDistSizes sz = tri_dist_sizes(d);
+        std::vector<T> winv(sz.winv + 1, nan_value<T>()), pan(sz.pan + 1, nan_value<T>()), pan2(sz.pan2 + 1, nan_value<T>()),
+            xb(sz.xb + 1, nan_value<T>()), wkh(sz.wkh + 1, nan_value<T>()), bt(sz.bt + 1, nan_value<T>());
+        TriDistWork<T> w{winv.data(), pan.data(), pan2.data(), xb.data(), wkh.data(), bt.data()};
+        DistHostOps<T> ops;
+        ops.row = &rows[pr];
+        ops.col = &cols[pc];
+        ops.me_row = pc;
+        ops.me_col = pr;
+        err[r] = triangular_solve_dist<T>(ops, d, *static_cast<const T*>(alpha), static_cast<const T*>(a[r]), lda[r],
+                                          static_cast<T*>(b[r]), ldb[r], w);
+        if (err[r] == 0 && ops.hazards)
+          err[r] = 9001;
+      });
+  for (auto& t : th)
+    t.join();
+  for (int e : err)
+    if (e)
+      return e;
+  return 0;
+}
+
 }  // namespace
 
 #define EMU_TYPED(X, T)                                                                                             \
@@ -381,6 +513,11 @@ int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void*
   }                                                                                                                 \
   int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
     return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
+  }                                                                                                                 \
+  int emu_triangular_solver_dist_##X(int P, int Q, int src_r, int src_c, char side, char uplo, char op, char diag,  \
+                                     int m, int n, int mb, int nb, const void* alpha, void* const* a,               \
+                                     const long long* lda, void* const* b, const long long* ldb) {                  \
+    return solve_dist<T>(P, Q, src_r, src_c, side, uplo, op, diag, m, n, mb, nb, alpha, a, lda, b, ldb);            \
   }
 
 extern "C" {
