@@ -15,6 +15,8 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
   cholesky_factorization<Backend::GPU, Device::GPU, T>(grid, blas::Uplo::Lower, a);
   triangular_solver<Backend::GPU, Device::GPU, T>(blas::Side::Left, blas::Uplo::Lower, blas::Op::NoTrans,
                                                   blas::Diag::NonUnit, T(1), a, b);
+  triangular_solver<Backend::GPU, Device::GPU, T>(grid, blas::Side::Right, blas::Uplo::Upper, blas::Op::ConjTrans,
+                                                  blas::Diag::Unit, T(1), a, b);
   eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, b, a);
   a.waitLocalTiles();
   b.waitLocalTiles();
