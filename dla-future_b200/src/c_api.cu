@@ -80,21 +80,35 @@ size_t elem_size(char t) { return t == 's' ? 4 : (t == 'z' ? 16 : 8); }
 int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   if (!g_initialized)
     die("dlaf_cholesky_factorization called before dlaf_initialize", -1);
-  if (d.i != 0 || d.j != 0)
-    die("sub-matrix offsets are not supported (desc.i, desc.j must be 0)", -1);  // cholesky.h:37-38
   if (d.m != d.n || d.mb != d.nb)
     die("cholesky_factorization needs a square matrix with square blocks", -1);  // factorization/cholesky.h:69-70
+  // Sub-matrix sub(A) = A(i : i+n, j : j+n) of the distributed matrix the descriptor describes. The reference stops at
+  // i = j = 0 (src/c_api/factorization/cholesky.h:37-38, src/c_api/utils.cpp:25-33); ScaLAPACK's p?potrf accepts
+  // tile-aligned offsets (IROFF = ICOFF = 0) and so does this build: a tile-aligned sub-matrix of a 2D block-cyclic
+  // matrix is itself 2D block-cyclic, with the source rank advanced by the tiles skipped, and on every rank its local
+  // block starts after the local tiles that precede the offset.
+  if (d.i < 0 || d.j < 0 || d.i % d.mb != 0 || d.j % d.nb != 0)
+    die("sub-matrix offsets must be non-negative multiples of the block size", d.i % d.mb != 0 ? d.i : d.j);
   auto git = g_grids.find(ctx);
   if (git == g_grids.end())
     die("no grid registered for this context", ctx);  // utils.cpp:55-69 terminates as well
   dlafb_grid_t grid = git->second;
-  const PlanKey key{ctx, type, uplo == 'u' ? 'U' : (uplo == 'l' ? 'L' : uplo), d.n, d.nb, d.isrc, d.jsrc};
+  if (d.isrc < 0 || d.isrc >= grid->P || d.jsrc < 0 || d.jsrc >= grid->Q)
+    die("source rank outside the grid", d.isrc);
+  const int i0 = d.i / d.mb, j0 = d.j / d.nb;
+  const int sub_isrc = (d.isrc + i0) % grid->P, sub_jsrc = (d.jsrc + j0) % grid->Q;
+  if (i0 != 0 || j0 != 0) {
+    const int64_t skip_r = dlafb_dist_next_local_tile_from_global(i0, grid->P, grid->pr, d.isrc) * d.mb;
+    const int64_t skip_c = dlafb_dist_next_local_tile_from_global(j0, grid->Q, grid->pc, d.jsrc) * d.nb;
+    a = static_cast<char*>(a) + ((size_t)skip_r + (size_t)skip_c * (size_t)d.ld) * elem_size(type);
+  }
+  const PlanKey key{ctx, type, uplo == 'u' ? 'U' : (uplo == 'l' ? 'L' : uplo), d.n, d.nb, sub_isrc, sub_jsrc};
   if (key.uplo != 'L' && key.uplo != 'U')
     die("uplo must be 'L' or 'U'", -1);
   PlanEntry& pe = g_plans[key];
   int e;
   if (!pe.plan) {
-    if ((e = dlafb_cholesky_plan_create(&pe.plan, grid, type, key.uplo, d.n, d.nb, d.isrc, d.jsrc)) != 0)
+    if ((e = dlafb_cholesky_plan_create(&pe.plan, grid, type, key.uplo, d.n, d.nb, sub_isrc, sub_jsrc)) != 0)
       die("plan creation failed", e);
     if (cudaStreamCreateWithFlags(&pe.stream, cudaStreamNonBlocking) != cudaSuccess)
       die("stream creation failed", -1);
@@ -137,8 +151,8 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
 void pxpotrf(char type, char uplo, int n, void* a, int ia, int ja, const int desca[9], int* info) {
   if (desca[0] != 1)
     die("only dense ScaLAPACK descriptors (desca[0] == 1) are supported", desca[0]);
-  if (ia != 1 || ja != 1)
-    die("ia and ja must be 1", ia);
+  if (ia < 1 || ja < 1)
+    die("ia and ja are 1-based", ia < 1 ? ia : ja);
   const DLAF_descriptor d = make_dlaf_descriptor(n, n, ia - 1, ja - 1, desca);
   const int r = cholesky(desca[1], type, uplo, a, d);
   if (info)
@@ -282,8 +296,8 @@ char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow, int mypcol) 
 
 struct DLAF_descriptor make_dlaf_descriptor(const int m, const int n, const int i, const int j,
                                             const int desc[9]) noexcept {
-  if (i != 0 || j != 0)
-    die("make_dlaf_descriptor: sub-matrix offsets must be 0", i);
+  if (i < 0 || j < 0)
+    die("make_dlaf_descriptor: negative sub-matrix offset", i < 0 ? i : j);
   struct DLAF_descriptor d = {m, n, desc[4], desc[5], desc[6], desc[7], i, j, desc[8]};
   return d;
 }

@@ -8,7 +8,7 @@ struct DLAF_descriptor {
   int nb;   /* column block size */
   int isrc; /* process row owning the first row */
   int jsrc; /* process column owning the first column */
-  int i;    /* first row of the sub-matrix: has to be 0 */
-  int j;    /* first column of the sub-matrix: has to be 0 */
+  int i;    /* first row of the sub-matrix (0-based): a multiple of mb (the reference requires 0) */
+  int j;    /* first column of the sub-matrix (0-based): a multiple of nb (the reference requires 0) */
   int ld;   /* leading dimension of the local matrix */
 };

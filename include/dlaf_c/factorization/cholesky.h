@@ -22,8 +22,10 @@ DLAF_EXTERN_C int dlaf_cholesky_factorization_c(const int dlaf_context, const ch
 DLAF_EXTERN_C int dlaf_cholesky_factorization_z(const int dlaf_context, const char uplo, dlaf_complex_z* a,
                                                 const struct DLAF_descriptor dlaf_desca) DLAF_NOEXCEPT;
 
-/* ScaLAPACK-like: ia == ja == 1, desca[0] == 1, desca[1] = context registered with
- * dlaf_create_grid_from_blacs_info (or returned by dlaf_create_grid). */
+/* ScaLAPACK-like: desca[0] == 1, desca[1] = context registered with dlaf_create_grid_from_blacs_info (or returned by
+ * dlaf_create_grid). Factorizes sub(A) = A(ia : ia+n-1, ja : ja+n-1); `a` points to the local block of the WHOLE
+ * distributed matrix. The reference requires ia == ja == 1 (src/c_api/factorization/cholesky.h:67-69); this build
+ * accepts what ScaLAPACK's p?potrf accepts: (ia - 1) a multiple of desca[4] and (ja - 1) a multiple of desca[5]. */
 DLAF_EXTERN_C void dlaf_pspotrf(const char uplo, const int n, float* a, const int ia, const int ja,
                                 const int desca[9], int* info) DLAF_NOEXCEPT;
 DLAF_EXTERN_C void dlaf_pdpotrf(const char uplo, const int n, double* a, const int ia, const int ja,
