@@ -84,7 +84,7 @@ def lib():
 
 
 from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
-from ._engine_api import (CholeskyPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverDistPlan,  # noqa: E402,F401
+from ._engine_api import (CholeskyPlan, GenToStdDistPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverDistPlan,  # noqa: E402,F401
                           TriangularSolverPlan, schedule_step)
 
 

@@ -64,6 +64,12 @@ ENGINE_API = {
     "dlafb_gen_to_std_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_gen_to_std_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
     "dlafb_gen_to_std_plan_destroy": (c_int, [c_vp]),
+    "dlafb_gen_to_std_dist_plan_create": (c_int, [ctypes.POINTER(c_vp), c_vp, c_char, c_char, c_i64, c_i64, c_int,
+                                                  c_int]),
+    "dlafb_gen_to_std_dist_plan_local_size": (c_int, [c_vp, P_i64, P_i64]),
+    "dlafb_gen_to_std_dist_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
+    "dlafb_gen_to_std_dist_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
+    "dlafb_gen_to_std_dist_plan_destroy": (c_int, [c_vp]),
 }
 
 
@@ -250,4 +256,28 @@ class GenToStdPlan:
     def close(self):
         if self.h:
             self.L.dlafb_gen_to_std_plan_destroy(self.h)
+            self.h = c_vp()
+
+
+class GenToStdDistPlan:
+    """generalized_to_standard(grid, ...) (include/dlafb_gen_to_std.h): collective over the grid, local blocks in and out."""
+
+    def __init__(self, L, grid, type_, uplo, n, nb, src=(0, 0)):
+        self.L = L
+        self.h = c_vp()
+        _ck(L.dlafb_gen_to_std_dist_plan_create(ctypes.byref(self.h), grid.h, type_.encode(), uplo.encode(), n, nb,
+                                                src[0], src[1]), "gen_to_std_dist_plan_create")
+        r, c = c_i64(), c_i64()
+        _ck(L.dlafb_gen_to_std_dist_plan_local_size(self.h, r, c), "gen_to_std_dist_plan_local_size")
+        self.local_rows, self.local_cols = r.value, c.value
+
+    def run(self, a_ptr, lda, f_ptr, ldf, stream):
+        _ck(self.L.dlafb_gen_to_std_dist_plan_run(self.h, a_ptr, lda, f_ptr, ldf, stream), "gen_to_std_dist_plan_run")
+
+    def workspace_bytes(self):
+        return self.L.dlafb_gen_to_std_dist_plan_workspace_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.dlafb_gen_to_std_dist_plan_destroy(self.h)
             self.h = c_vp()

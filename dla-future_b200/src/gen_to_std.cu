@@ -5,7 +5,9 @@
 
 #include <new>
 
+#include "dist_device_ops.h"
 #include "dlafb_gen_to_std.h"
+#include "gen_to_std_dist.h"
 #include "tile_ops.cuh"
 
 namespace dlafb {
@@ -60,6 +62,28 @@ int g2s_run_typed(G2sPlan& p, void* a, long long lda, const void* f, long long l
   w.ldc = g2s_ldp(p.n);
   G2sDeviceOps<T> ops{s};
   return gen_to_std<T>(ops, p.uplo, p.n, p.nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+}
+
+struct G2sDistPlan {
+  char type;
+  G2sDistDesc d;
+  dlafb_grid* grid;
+  size_t elem;
+  void* base = nullptr;
+  size_t off[7] = {};
+  size_t bytes = 0;
+  ~G2sDistPlan() { cudaFree(base); }
+};
+
+template <class T>
+int g2s_dist_run_typed(G2sDistPlan& p, void* a, long long lda, const void* f, long long ldf, cudaStream_t s) {
+  char* b = static_cast<char*>(p.base);
+  G2sDistWork<T> w{reinterpret_cast<T*>(b + p.off[0]), reinterpret_cast<T*>(b + p.off[1]),
+                   reinterpret_cast<T*>(b + p.off[2]), reinterpret_cast<T*>(b + p.off[3]),
+                   reinterpret_cast<T*>(b + p.off[4]), reinterpret_cast<T*>(b + p.off[5]),
+                   reinterpret_cast<T*>(b + p.off[6])};
+  DistDeviceOps<T> ops{s, p.grid};
+  return gen_to_std_dist<T>(ops, p.d, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
 }
 
 }  // namespace
@@ -130,6 +154,76 @@ size_t dlafb_gen_to_std_plan_workspace_bytes(dlafb_gen_to_std_plan_t plan) {
 
 int dlafb_gen_to_std_plan_destroy(dlafb_gen_to_std_plan_t plan) {
   delete reinterpret_cast<G2sPlan*>(plan);
+  return 0;
+}
+
+int dlafb_gen_to_std_dist_plan_create(dlafb_gen_to_std_dist_plan_t* out, dlafb_grid_t grid, char type, char uplo,
+                                      int64_t n, int64_t nb, int src_r, int src_c) {
+  if (!out || !grid || (type != 's' && type != 'd' && type != 'c' && type != 'z') || (uplo != 'L' && uplo != 'U') ||
+      n < 0 || nb < 1 || n > (1LL << 30) || nb > (1 << 14) || src_r < 0 || src_r >= grid->P || src_c < 0 ||
+      src_c >= grid->Q)
+    return -1;
+  G2sDistPlan* p = new (std::nothrow) G2sDistPlan;
+  if (!p)
+    return (int)cudaErrorMemoryAllocation;
+  p->type = type;
+  p->grid = grid;
+  p->d = G2sDistDesc{uplo, (int)n, (int)nb, grid->P, grid->Q, grid->pr, grid->pc, src_r, src_c};
+  p->elem = type == 's' ? 4 : type == 'z' ? 16 : 8;
+  if (n > 0) {
+    const G2sDistSizes sz = g2s_dist_sizes(p->d);
+    const size_t parts[7] = {sz.winv, sz.dk, sz.tmp, sz.xr, sz.ytiles, sz.acopy, sz.lcopy};
+    size_t at = 0;
+    for (int i = 0; i < 7; ++i) {
+      p->off[i] = at;
+      at = align_up(at + (parts[i] > 0 ? parts[i] : 1) * p->elem);
+    }
+    p->bytes = at;
+    const cudaError_t e = cudaMalloc(&p->base, p->bytes);
+    if (e != cudaSuccess) {
+      delete p;
+      return (int)e;
+    }
+  }
+  *out = reinterpret_cast<dlafb_gen_to_std_dist_plan_t>(p);
+  return 0;
+}
+
+int dlafb_gen_to_std_dist_plan_local_size(dlafb_gen_to_std_dist_plan_t plan, int64_t* rows, int64_t* cols) {
+  G2sDistPlan* p = reinterpret_cast<G2sDistPlan*>(plan);
+  if (!p)
+    return -1;
+  if (rows) *rows = Dist1D{p->d.n, p->d.nb, p->d.P, p->d.pr, p->d.src_r}.local_size();
+  if (cols) *cols = Dist1D{p->d.n, p->d.nb, p->d.Q, p->d.pc, p->d.src_c}.local_size();
+  return 0;
+}
+
+int dlafb_gen_to_std_dist_plan_run(dlafb_gen_to_std_dist_plan_t plan, void* a, int64_t lda, const void* factor,
+                                   int64_t ldf, void* stream) {
+  G2sDistPlan* p = reinterpret_cast<G2sDistPlan*>(plan);
+  if (!p)
+    return -1;
+  if (p->d.n == 0)
+    return 0;
+  const int64_t rows = Dist1D{p->d.n, p->d.nb, p->d.P, p->d.pr, p->d.src_r}.local_size();
+  const int64_t cols = Dist1D{p->d.n, p->d.nb, p->d.Q, p->d.pc, p->d.src_c}.local_size();
+  if (rows > 0 && cols > 0 && (!a || !factor || lda < rows || ldf < rows))
+    return -1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->type) {
+    case 's': return g2s_dist_run_typed<float>(*p, a, lda, factor, ldf, s);
+    case 'd': return g2s_dist_run_typed<double>(*p, a, lda, factor, ldf, s);
+    case 'c': return g2s_dist_run_typed<float2>(*p, a, lda, factor, ldf, s);
+    default: return g2s_dist_run_typed<double2>(*p, a, lda, factor, ldf, s);
+  }
+}
+
+size_t dlafb_gen_to_std_dist_plan_workspace_bytes(dlafb_gen_to_std_dist_plan_t plan) {
+  return plan ? reinterpret_cast<G2sDistPlan*>(plan)->bytes : 0;
+}
+
+int dlafb_gen_to_std_dist_plan_destroy(dlafb_gen_to_std_dist_plan_t plan) {
+  delete reinterpret_cast<G2sDistPlan*>(plan);
   return 0;
 }
 

@@ -49,6 +49,10 @@ struct TriDistDesc {
   int m, n;    // B is m x n (global); A is m x m (side 'L') or n x n (side 'R')
   int mb, nb;  // tile size of B; A has square tiles of mb (side 'L') or nb (side 'R')
   int P, Q, pr, pc, src_r, src_c;
+  // 1 (side 'L', uplo 'L', op 'N', mb == nb only): B is the strictly-lower block trapezoid of a square matrix - at
+  // step k only the columns of the column tiles before k take part (gen_to_std_dist.h solves all its column panels
+  // side by side this way); the other tiles of B are neither read nor written.
+  int trapezoid = 0;
 };
 
 struct TriDistGeom {
@@ -212,27 +216,38 @@ int triangular_solve_dist(Ops& ops, const TriDistDesc& d, T alpha, const T* A, l
         if (d.Q > 1 && (e = ops.bcast_row(qc_k, w.pan, (size_t)ldap * wk)) != 0)
           return e;
       }
-      if (lcols <= 0)
-        continue;
-      const long long ldx = tri_dist_ld(lcols);
       if (bcast_pattern) {
+        // columns of B that take part in this step (all of them, or the tiles before k of a block trapezoid)
+        int nc = lcols;
+        if (d.trapezoid) {
+          const long long lim = g.cols.next_local(k) * (long long)t;
+          nc = lim < lcols ? (int)lim : lcols;
+        }
+        if (nc <= 0)
+          continue;
+        const long long ldx = tri_dist_ld(nc);
         if (own_row) {
-          if ((e = ops.transpose(wk, lcols, bk, ldb, w.xb, ldx, 1, 'G')) != 0)  // xb = B_k^H
+          if ((e = ops.transpose(wk, nc, bk, ldb, w.xb, ldx, 1, 'G')) != 0)  // xb = B_k^H
             return e;
-          if ((e = ops.gemm_nt(wk, lcols, wk, R(1), w.pan + diag_off, ldap, w.xb, ldx, R(0), bk, ldb, 0)) != 0)
+          if ((e = ops.gemm_nt(wk, nc, wk, R(1), w.pan + diag_off, ldap, w.xb, ldx, R(0), bk, ldb, 0)) != 0)
             return e;
-          if (more && (e = ops.transpose(wk, lcols, bk, ldb, w.xb, ldx, 1, 'G')) != 0)  // xb = X_k^H
+          if (more && (e = ops.transpose(wk, nc, bk, ldb, w.xb, ldx, 1, 'G')) != 0)  // xb = X_k^H
             return e;
         }
         if (!more)
           continue;
         if (d.P > 1 && (e = ops.bcast_col(pr_k, w.xb, (size_t)ldx * wk)) != 0)
           return e;
-        if (rem_rows > 0 && (e = ops.gemm_nt(rem_rows, lcols, wk, R(-1), w.pan + (rem_begin - r_begin), ldap, w.xb, ldx,
+        if (rem_rows > 0 && (e = ops.gemm_nt(rem_rows, nc, wk, R(-1), w.pan + (rem_begin - r_begin), ldap, w.xb, ldx,
                                              R(1), B + rem_begin, ldb, 0)) != 0)
           return e;
+        continue;
       }
-      else {
+      if (lcols <= 0)
+        continue;
+      const long long ldx = tri_dist_ld(lcols);
+      {
+        // reduce pattern:
         // xb (lcols x wk) = B_k^H - sum over the solved local rows of X^H A(:, k), reduced onto the owners of block k
         const long long ldpt = tri_dist_ld(t);
         if (rem_rows > 0 &&

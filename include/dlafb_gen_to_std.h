@@ -37,6 +37,27 @@ size_t dlafb_gen_to_std_plan_workspace_bytes(dlafb_gen_to_std_plan_t plan);
 /* The caller synchronises with the last run first. */
 int dlafb_gen_to_std_plan_destroy(dlafb_gen_to_std_plan_t plan);
 
+/* ---- distributed over a P x Q grid (dlafb_engine.h: dlafb_grid_t), one process per GPU ----
+ * Reference: generalized_to_standard(grid, uplo, mat_a, mat_b), include/dlaf/eigensolver/gen_to_std.h:79-140,
+ * algorithms include/dlaf/eigensolver/gen_to_std/impl.h:286-505 (call_L), :572-771 (call_U).
+ * A and the factor are distributed 2D block-cyclically with nb x nb tiles and source rank (src_r, src_c). Collective:
+ * every rank creates the plan and calls run with its local blocks. The grid must outlive the plan. */
+typedef struct dlafb_gen_to_std_dist_plan* dlafb_gen_to_std_dist_plan_t;
+#ifndef DLAFB_ENGINE_H
+typedef struct dlafb_grid* dlafb_grid_t;
+#endif
+
+int dlafb_gen_to_std_dist_plan_create(dlafb_gen_to_std_dist_plan_t* plan, dlafb_grid_t grid, char type, char uplo,
+                                      int64_t n, int64_t nb, int src_r, int src_c);
+/* Local block dimensions of this rank (the same for A and for the factor). */
+int dlafb_gen_to_std_dist_plan_local_size(dlafb_gen_to_std_dist_plan_t plan, int64_t* rows, int64_t* cols);
+/* In place on the local block `a`; `factor` is never written. Asynchronous: local work and the NCCL broadcasts along
+ * the grid's rows and columns are enqueued on `stream` in order. Collective. */
+int dlafb_gen_to_std_dist_plan_run(dlafb_gen_to_std_dist_plan_t plan, void* a, int64_t lda, const void* factor,
+                                   int64_t ldf, void* stream);
+size_t dlafb_gen_to_std_dist_plan_workspace_bytes(dlafb_gen_to_std_dist_plan_t plan);
+int dlafb_gen_to_std_dist_plan_destroy(dlafb_gen_to_std_dist_plan_t plan);
+
 #ifdef __cplusplus
 }
 #endif

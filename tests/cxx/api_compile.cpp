@@ -18,6 +18,7 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
   triangular_solver<Backend::GPU, Device::GPU, T>(grid, blas::Side::Right, blas::Uplo::Upper, blas::Op::ConjTrans,
                                                   blas::Diag::Unit, T(1), a, b);
   eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, b, a);
+  eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(grid, blas::Uplo::Upper, b, a);
   a.waitLocalTiles();
   b.waitLocalTiles();
 }

@@ -22,6 +22,7 @@
 #include <thread>
 
 #include "gen_to_std.h"
+#include "gen_to_std_dist.h"
 #include "triangular_solver.h"
 #include "triangular_solver_dist.h"
 
@@ -496,6 +497,50 @@ int solve_dist(int P, int Q, int src_r, int src_c, char side, char uplo, char op
   return 0;
 }
 
+// Distributed generalized-to-standard reduction for all the ranks of a simulated grid.
+template <class T>
+int gen_to_std_dist_emu(int P, int Q, int src_r, int src_c, char uplo, int n, int nb, void* const* a,
+                        const long long* lda, void* const* f, const long long* ldf) {
+  std::vector<SimComm> rows(P), cols(Q);
+  for (auto& c : rows) {
+    c.size = Q;
+    c.ptr.assign(Q, nullptr);
+    c.cnt.assign(Q, 0);
+  }
+  for (auto& c : cols) {
+    c.size = P;
+    c.ptr.assign(P, nullptr);
+    c.cnt.assign(P, 0);
+  }
+  std::vector<int> err(P * Q, 0);
+  std::vector<std::thread> th;
+  for (int pr = 0; pr < P; ++pr)
+    for (int pc = 0; pc < Q; ++pc)
+      th.emplace_back([&, pr, pc] {
+        const int r = pr * Q + pc;
+        G2sDistDesc d{uplo, n, nb, P, Q, pr, pc, src_r, src_c};
+        const G2sDistSizes sz = g2s_dist_sizes(d);
+        std::vector<T> winv(sz.winv + 1, nan_value<T>()), dk(sz.dk + 1, nan_value<T>()), tmp(sz.tmp + 1, nan_value<T>()),
+            xr(sz.xr + 1, nan_value<T>()), yt(sz.ytiles + 1, nan_value<T>()), ac(sz.acopy + 1, nan_value<T>()),
+            lc(sz.lcopy + 1, nan_value<T>());
+        G2sDistWork<T> w{winv.data(), dk.data(), tmp.data(), xr.data(), yt.data(), ac.data(), lc.data()};
+        DistHostOps<T> ops;
+        ops.row = &rows[pr];
+        ops.col = &cols[pc];
+        ops.me_row = pc;
+        ops.me_col = pr;
+        err[r] = gen_to_std_dist<T>(ops, d, static_cast<T*>(a[r]), lda[r], static_cast<const T*>(f[r]), ldf[r], w);
+        if (err[r] == 0 && ops.hazards)
+          err[r] = 9001;
+      });
+  for (auto& t : th)
+    t.join();
+  for (int e : err)
+    if (e)
+      return e;
+  return 0;
+}
+
 }  // namespace
 
 #define EMU_TYPED(X, T)                                                                                             \
@@ -513,6 +558,10 @@ int solve_dist(int P, int Q, int src_r, int src_c, char side, char uplo, char op
   }                                                                                                                 \
   int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
     return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
+  }                                                                                                                 \
+  int emu_gen_to_std_dist_##X(int P, int Q, int src_r, int src_c, char uplo, int n, int nb, void* const* a,         \
+                              const long long* lda, void* const* f, const long long* ldf) {                          \
+    return gen_to_std_dist_emu<T>(P, Q, src_r, src_c, uplo, n, nb, a, lda, f, ldf);                                  \
   }                                                                                                                 \
   int emu_triangular_solver_dist_##X(int P, int Q, int src_r, int src_c, char side, char uplo, char op, char diag,  \
                                      int m, int n, int mb, int nb, const void* alpha, void* const* a,               \
