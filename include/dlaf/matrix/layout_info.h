@@ -22,6 +22,28 @@ public:
   SizeType ldTile() const noexcept { return ld_tile_; }
   const LocalElementSize& size() const noexcept { return size_; }
   const TileElementSize& block_size() const noexcept { return block_; }
+  const TileElementSize& blockSize() const noexcept { return block_; }
+  LocalTileSize nr_tiles() const noexcept {
+    return {(size_.rows() + block_.rows() - 1) / block_.rows(), (size_.cols() + block_.cols() - 1) / block_.cols()};
+  }
+  LocalTileSize nrTiles() const noexcept { return nr_tiles(); }
+  /// Size of local tile @p index (edge tiles are smaller; layout_info.h:96-103).
+  TileElementSize tile_size_of(const LocalTileIndex& index) const noexcept {
+    const SizeType r = size_.rows() - index.row() * block_.rows(), c = size_.cols() - index.col() * block_.cols();
+    return {r < block_.rows() ? r : block_.rows(), c < block_.cols() ? c : block_.cols()};
+  }
+  TileElementSize tileSize(const LocalTileIndex& index) const noexcept { return tile_size_of(index); }
+  /// Minimum number of elements a tile occupies (layout_info.h:78-94).
+  SizeType min_tile_mem_size(const TileElementSize& tile_size) const noexcept {
+    return tile_size.isEmpty() ? 0 : tile_size.rows() + ld_tile_ * (tile_size.cols() - 1);
+  }
+  SizeType minTileMemSize(const TileElementSize& tile_size) const noexcept { return min_tile_mem_size(tile_size); }
+  SizeType minTileMemSize(const LocalTileIndex& index) const noexcept { return min_tile_mem_size(tile_size_of(index)); }
+  bool operator==(const LayoutInfo& o) const noexcept {
+    return size_ == o.size_ && block_ == o.block_ && ld_tile_ == o.ld_tile_ && off_row_ == o.off_row_ &&
+           off_col_ == o.off_col_;
+  }
+  bool operator!=(const LayoutInfo& o) const noexcept { return !(*this == o); }
   bool is_col_major() const noexcept { return off_row_ == block_.rows() && off_col_ == block_.cols() * ld_tile_; }
 
   /// Minimum number of elements the memory has to hold (layout_info.cpp:40-60).

@@ -3,6 +3,7 @@
 
   test/unit/matrix/test_util_distribution.cpp:43-62   `tests` of UtilDistribution.IndexConversion
   test/unit/matrix/test_distribution.cpp:40-104       `tests_constructor` of DistributionTest.*
+  test/unit/matrix/test_layout_info.cpp:23-34, :91-99 `values` of LayoutInfoTest.Constructor, `comp_values` of .ComparisonOperator
 
 Only the numbers are taken (test DATA, the golden vectors of SURVEY.md §8c item 4), no code.
     python tests/golden/extract_reference_tables.py [/root/reference]
@@ -55,7 +56,19 @@ def main():
     with open(os.path.join(HERE, "distribution_constructor.json"), "w") as f:
         json.dump({"source": "test/unit/matrix/test_distribution.cpp:40-104 (DLA-Future v0.6.0)", "keys": keys,
                    "rows": rows}, f, indent=0)
-    print("wrote 2 fixtures")
+    src = open(os.path.join(ref, "test/unit/matrix/test_layout_info.cpp")).read()
+    rows = table(src, "\n    values(")
+    assert all(len(r) == 8 for r in rows) and len(rows) >= 11
+    comp = table(src.replace("true", "1").replace("false", "0"), "comp_values(")
+    assert all(len(r) == 8 for r in comp) and len(comp) >= 6
+    with open(os.path.join(HERE, "layout_info.json"), "w") as f:
+        json.dump({"source": "test/unit/matrix/test_layout_info.cpp:23-34, :91-99 (DLA-Future v0.6.0)",
+                   "keys": ["rows", "cols", "block_rows", "block_cols", "ld", "row_offset", "col_offset", "min_memory"],
+                   "rows": rows,
+                   "comparison_keys": ["rows", "cols", "block_rows", "block_cols", "ld", "row_offset", "col_offset",
+                                       "equal_to_25_25_5_5_50_8_1000"],
+                   "comparison_rows": comp}, f, indent=0)
+    print("wrote 3 fixtures")
 
 
 if __name__ == "__main__":
