@@ -1,6 +1,6 @@
 # Builds the product library (CUDA kernels + C++ host layer + C API) in-tree for sm_100a.
 #   make            -> dla-future_b200/lib/libdlaf_b200.so
-#   make miniapp    -> dla-future_b200/bin/miniapp_cholesky
+#   make miniapp    -> dla-future_b200/bin/miniapp_{cholesky,triangular_solver,gen_to_std}
 #   make oracle     -> oracle/_build/liboracle.so (test infrastructure only)
 #   make emu        -> tests/emu/_build/libsolver_emu.so (test infrastructure only)
 NVCC      ?= /usr/local/cuda/bin/nvcc
@@ -30,7 +30,11 @@ $(LIBDIR)/libdlaf_b200.so: $(OBJS)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart -lnccl
 
-miniapp: $(BINDIR)/miniapp_cholesky
+miniapp: $(BINDIR)/miniapp_cholesky $(BINDIR)/miniapp_triangular_solver $(BINDIR)/miniapp_gen_to_std
+
+$(BINDIR)/miniapp_triangular_solver $(BINDIR)/miniapp_gen_to_std: $(BINDIR)/%: miniapp/%.cpp miniapp/miniapp_common.h $(LIBDIR)/libdlaf_b200.so $(HDRS)
+	@mkdir -p $(BINDIR)
+	$(NVCC) $(ARCH) -O2 -std=c++17 -Iinclude -Iinclude/dlafb_mpi_shim -o $@ $< -L$(LIBDIR) -ldlaf_b200 -Xlinker -rpath -Xlinker '$$ORIGIN/../lib' -lcudart
 
 $(BINDIR)/miniapp_cholesky: miniapp/miniapp_cholesky.cpp $(LIBDIR)/libdlaf_b200.so $(HDRS)
 	@mkdir -p $(BINDIR)
