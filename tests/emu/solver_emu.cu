@@ -39,6 +39,31 @@ T nan_value() {
     return q;
 }
 
+template <class T>
+bool is_nan_value(T v) {
+  if constexpr (Tr<T>::is_complex)
+    return v.x != v.x && v.y != v.y;
+  else
+    return v != v;
+}
+
+// A workspace part as the device plan would allocate it (exactly `n` elements) followed by a guard zone: anything the
+// algorithm writes past the end of a part shows up as a damaged guard (error 9300) instead of silent corruption.
+template <class T>
+struct Guarded {
+  static constexpr size_t kGuard = 64;
+  std::vector<T> v;
+  size_t n;
+  explicit Guarded(size_t elems) : v(elems + kGuard, nan_value<T>()), n(elems) {}
+  T* data() { return v.data(); }
+  bool intact() const {
+    for (size_t i = n; i < v.size(); ++i)
+      if (!is_nan_value<T>(v[i]))
+        return false;
+    return true;
+  }
+};
+
 // do the element sets {p + i + j*ld : i < rows, j < cols} of two operands intersect?
 template <class T>
 bool overlap(const T* a, long long lda, int ra, int ca, const T* b, long long ldb, int rb, int cb) {
@@ -360,14 +385,15 @@ int inverse(int upper, int unit, int n, int nb, const void* t, long long ldt, vo
 // Generalized-to-standard reduction: the product's algorithm template over the host executor, NaN-filled workspaces.
 template <class T>
 int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {
-  std::vector<T> winv(g2s_winv_elems(n, nb), nan_value<T>());
-  std::vector<T> akk(g2s_tile_elems(nb), nan_value<T>()), tmp(g2s_tile_elems(nb), nan_value<T>());
-  std::vector<T> pa(g2s_panel_elems(n, nb), nan_value<T>()), pb(g2s_panel_elems(n, nb), nan_value<T>());
-  std::vector<T> ac(g2s_copy_elems(n, uplo), nan_value<T>()), lc(g2s_copy_elems(n, uplo), nan_value<T>());
+  Guarded<T> winv(g2s_winv_elems(n, nb)), akk(g2s_tile_elems(nb)), tmp(g2s_tile_elems(nb)), pa(g2s_panel_elems(n, nb)),
+      pb(g2s_panel_elems(n, nb)), ac(g2s_copy_elems(n, uplo)), lc(g2s_copy_elems(n, uplo));
   GenToStdWork<T> w{winv.data(), akk.data(), tmp.data(), g2s_even(nb), pa.data(), pb.data(), g2s_ldp(n),
                     ac.data(), lc.data(), g2s_ldp(n)};
   HostOps<T> ops;
-  return gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  const int e = gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  if (e == 0 && !(winv.intact() && akk.intact() && tmp.intact() && pa.intact() && pb.intact() && ac.intact() && lc.intact()))
+    return 9300;
+  return e;
 }
 
 // ---- simulated grid: one host thread per rank, collectives through shared memory -------------------------------
@@ -476,8 +502,7 @@ int solve_dist(int P, int Q, int src_r, int src_c, char side, char uplo, char op
         const int r = pr * Q + pc;
         TriDistDesc d{side, uplo, op, diag, m, n, mb, nb, P, Q, pr, pc, src_r, src_c};
         const TriDistSizes sz = tri_dist_sizes(d);
-        std::vector<T> winv(sz.winv + 1, nan_value<T>()), pan(sz.pan + 1, nan_value<T>()), pan2(sz.pan2 + 1, nan_value<T>()),
-            xb(sz.xb + 1, nan_value<T>()), wkh(sz.wkh + 1, nan_value<T>()), bt(sz.bt + 1, nan_value<T>());
+        Guarded<T> winv(sz.winv), pan(sz.pan), pan2(sz.pan2), xb(sz.xb), wkh(sz.wkh), bt(sz.bt);
         TriDistWork<T> w{winv.data(), pan.data(), pan2.data(), xb.data(), wkh.data(), bt.data()};
         DistHostOps<T> ops;
         ops.row = &rows[pr];
@@ -488,6 +513,8 @@ int solve_dist(int P, int Q, int src_r, int src_c, char side, char uplo, char op
                                           static_cast<T*>(b[r]), ldb[r], w);
         if (err[r] == 0 && ops.hazards)
           err[r] = 9001;
+        if (err[r] == 0 && !(winv.intact() && pan.intact() && pan2.intact() && xb.intact() && wkh.intact() && bt.intact()))
+          err[r] = 9300;
       });
   for (auto& t : th)
     t.join();
@@ -520,9 +547,7 @@ int gen_to_std_dist_emu(int P, int Q, int src_r, int src_c, char uplo, int n, in
         const int r = pr * Q + pc;
         G2sDistDesc d{uplo, n, nb, P, Q, pr, pc, src_r, src_c};
         const G2sDistSizes sz = g2s_dist_sizes(d);
-        std::vector<T> winv(sz.winv + 1, nan_value<T>()), dk(sz.dk + 1, nan_value<T>()), tmp(sz.tmp + 1, nan_value<T>()),
-            xr(sz.xr + 1, nan_value<T>()), yt(sz.ytiles + 1, nan_value<T>()), ac(sz.acopy + 1, nan_value<T>()),
-            lc(sz.lcopy + 1, nan_value<T>());
+        Guarded<T> winv(sz.winv), dk(sz.dk), tmp(sz.tmp), xr(sz.xr), yt(sz.ytiles), ac(sz.acopy), lc(sz.lcopy);
         G2sDistWork<T> w{winv.data(), dk.data(), tmp.data(), xr.data(), yt.data(), ac.data(), lc.data()};
         DistHostOps<T> ops;
         ops.row = &rows[pr];
@@ -532,6 +557,9 @@ int gen_to_std_dist_emu(int P, int Q, int src_r, int src_c, char uplo, int n, in
         err[r] = gen_to_std_dist<T>(ops, d, static_cast<T*>(a[r]), lda[r], static_cast<const T*>(f[r]), ldf[r], w);
         if (err[r] == 0 && ops.hazards)
           err[r] = 9001;
+        if (err[r] == 0 && !(winv.intact() && dk.intact() && tmp.intact() && xr.intact() && yt.intact() && ac.intact() &&
+                             lc.intact()))
+          err[r] = 9300;
       });
   for (auto& t : th)
     t.join();
