@@ -126,3 +126,83 @@ def test_random_against_lapack(emu, x, grid, src, side, uplo, op):
     want = sla.solve(opa, alpha * b) if side == "L" else sla.solve(opa.T, (alpha * b).T).T
     got = run(emu, x, grid, src, side, uplo, op, "N", alpha, a, b, mb, nb, pad=1)
     assert np.abs(got - want).max() <= 1e-11 * np.abs(want).max() * max(m, n)
+
+
+MUTATIONS = {
+    # a non-owner of block k adds its partial sum to whatever its buffer held instead of overwriting it
+    "reduce_accumulates_into_garbage": ("triangular_solver_dist.h", "ldar, own_col ? R(1) : R(0), w.xb, ldx)", "ldar, R(1), w.xb, ldx)"),
+    # the solved block travels down the grid column from the wrong rank row
+    "bcast_from_wrong_root": ("triangular_solver_dist.h", "ops.bcast_col(pr_k, w.xb, (size_t)ldx * wk)",
+                              "ops.bcast_col((pr_k + 1) % d.P, w.xb, (size_t)ldx * wk)"),
+    # the update forgets that the panel starts at the first row beyond... the diagonal tile, not at the local origin
+    "panel_offset_dropped": ("triangular_solver_dist.h", "R(-1), w.pan + (rem_begin - r_begin), ldap, w.xb, ldx,", "R(-1), w.pan, ldap, w.xb, ldx,"),
+    # the column panel of the distributed reduction is sent without swapping its halves
+    "g2s_column_panel_not_swapped": ("gen_to_std_dist.h", "ops.lacpy('G', wj, nb, xl + rloc, ldxr, slot, ldk)",
+                                     "ops.lacpy('G', wj, nb, xp + rloc, ldxr, slot, ldk)"),
+}
+
+
+@pytest.mark.parametrize("name", sorted(MUTATIONS))
+def test_simulated_grid_catches_seeded_faults(emu, name):
+    """The simulated grid is only worth something if it fails when the distributed logic is wrong: seed a fault into a
+    copy of the algorithm header, rebuild the emulation against it, and expect an error code or a wrong answer."""
+    fname, old, new = MUTATIONS[name]
+    src = open(os.path.join(ROOT, "dla-future_b200", "src", fname)).read()
+    assert src.count(old) == 1, (name, src.count(old))
+    mut_dir = os.path.join(ROOT, "tests", "emu", "_build", "mutd_" + name)
+    os.makedirs(mut_dir, exist_ok=True)
+    # the two headers include each other with quotes: keep the pair together in the mutated directory
+    for h in ("triangular_solver_dist.h", "gen_to_std_dist.h"):
+        text = open(os.path.join(ROOT, "dla-future_b200", "src", h)).read()
+        with open(os.path.join(mut_dir, h), "w") as f:
+            f.write(text.replace(old, new) if h == fname else text)
+    so = os.path.join(mut_dir, "libsolver_emu_mut.so")
+    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O1", "-std=c++17", "-Wno-deprecated-gpu-targets", "-shared",
+                           "-Xcompiler", "-fPIC,-pthread", "-I" + mut_dir,
+                           "-I" + os.path.join(ROOT, "dla-future_b200", "csrc"),
+                           "-I" + os.path.join(ROOT, "dla-future_b200", "src"), "-o", so,
+                           os.path.join(ROOT, "tests", "emu", "solver_emu.cu")])
+    lib = ctypes.CDLL(so)
+    rng = np.random.default_rng(3)
+    caught = 0
+    if fname == "triangular_solver_dist.h":
+        f = lib.emu_triangular_solver_dist_d
+        f.argtypes = getattr(emu, "emu_triangular_solver_dist_d").argtypes
+        f.restype = ctypes.c_int
+        m, n, mb, nb = 37, 29, 5, 4
+        for side, uplo, op in (("L", "L", "N"), ("R", "L", "C"), ("L", "U", "C"), ("R", "U", "N")):
+            na = m if side == "L" else n
+            a = (rng.standard_normal((na, na)) / np.sqrt(na) + 2 * np.eye(na)).astype(np.float64)
+            b = rng.standard_normal((m, n))
+            tri = np.tril(a) if uplo == "L" else np.triu(a)
+            opa = tri if op == "N" else tri.T
+            want = sla.solve(opa, b) if side == "L" else sla.solve(opa.T, b.T).T
+
+            class Fake:
+                pass
+            fake = Fake()
+            setattr(fake, "emu_triangular_solver_dist_d", f)
+            try:
+                got = run(fake, "d", (2, 3), (1, 1), side, uplo, op, "N", 1.0, a, b, mb, nb)
+                caught += int(not (np.abs(got - want).max() <= 1e-9))
+            except AssertionError:
+                caught += 1
+    else:
+        import test_gen_to_std_dist_emu as g2s
+        f = lib.emu_gen_to_std_dist_d
+        f.argtypes = [ctypes.c_int] * 4 + [ctypes.c_char] + [ctypes.c_int] * 2 + [
+            ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_longlong),
+            ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_longlong)]
+        f.restype = ctypes.c_int
+
+        class Fake:
+            pass
+        fake = Fake()
+        setattr(fake, "emu_gen_to_std_dist_d", f)
+        t, a, res = orc.gen_to_std_setters(32, "L", np.float64)
+        try:
+            got = g2s.run(fake, "d", (2, 3), (1, 1), "L", a, t, 5)
+            caught += int(orc.check_near(got, res, 10 * 33 * orc.type_error(np.float64), 0.0) != 0)
+        except AssertionError:
+            caught += 1
+    assert caught > 0
