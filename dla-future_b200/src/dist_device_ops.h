@@ -73,6 +73,9 @@ struct DistDeviceOps {
   int reduce_row(int root, T* p, size_t count) {
     return nccl_code(ncclReduce(p, p, count * NcclType<T>::mult, NcclType<T>::value, ncclSum, root, g->row, s));
   }
+  // collectives between group_begin / group_end are launched together (ncclGroupStart / ncclGroupEnd)
+  int group_begin() { return nccl_code(ncclGroupStart()); }
+  int group_end() { return nccl_code(ncclGroupEnd()); }
   int reduce_col(int root, T* p, size_t count) {
     return nccl_code(ncclReduce(p, p, count * NcclType<T>::mult, NcclType<T>::value, ncclSum, root, g->col, s));
   }

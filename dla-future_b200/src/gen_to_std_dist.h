@@ -99,6 +99,8 @@ struct AxesSwappedOps {
   int bcast_col(int root, T* p, size_t count) { return o.bcast_row(root, p, count); }
   int reduce_row(int root, T* p, size_t count) { return o.reduce_col(root, p, count); }
   int reduce_col(int root, T* p, size_t count) { return o.reduce_row(root, p, count); }
+  int group_begin() { return o.group_begin(); }
+  int group_end() { return o.group_end(); }
 };
 
 // Lower algorithm on the grid (P, Q, pr, pc, src_r, src_c) as given.
@@ -177,17 +179,26 @@ int gen_to_std_dist_lower(Ops& ops, int n, int nb, int P, int Q, int pr, int pc,
     const int jl1 = (int)DC.next_local(k + 1);
     for (int jl = jl1; jl < nlc; ++jl) {
       const int j = (int)DC.global_of(jl);
+      if (pr != DR.owner(j))
+        continue;
       const int wj = (int)DC.tile_size(j);
-      const int root = DR.owner(j);
       T* slot = w.ytiles + (size_t)(jl - jl1) * slot_elems;
-      if (pr == root) {
-        const long long rloc = DR.local_of(j) * nb - r_begin;
-        if ((e = ops.lacpy('G', wj, nb, xl + rloc, ldxr, slot, ldk)) != 0)
-          return e;
-        if ((e = ops.lacpy('G', wj, nb, xp + rloc, ldxr, slot + (long long)nb * ldk, ldk)) != 0)
+      const long long rloc = DR.local_of(j) * nb - r_begin;
+      if ((e = ops.lacpy('G', wj, nb, xl + rloc, ldxr, slot, ldk)) != 0)
+        return e;
+      if ((e = ops.lacpy('G', wj, nb, xp + rloc, ldxr, slot + (long long)nb * ldk, ldk)) != 0)
+        return e;
+    }
+    if (P > 1 && jl1 < nlc) {
+      // one grouped launch for the whole column panel (the tiles have different roots)
+      if ((e = ops.group_begin()) != 0)
+        return e;
+      for (int jl = jl1; jl < nlc; ++jl) {
+        const int root = DR.owner(DC.global_of(jl));
+        if ((e = ops.bcast_col(root, w.ytiles + (size_t)(jl - jl1) * slot_elems, slot_elems)) != 0)
           return e;
       }
-      if (P > 1 && (e = ops.bcast_col(root, slot, slot_elems)) != 0)
+      if ((e = ops.group_end()) != 0)
         return e;
     }
     // trailing update of the local tiles (i, j), i >= j > k

@@ -149,6 +149,7 @@ int tri_dist_gemm_ksplit(Ops& ops, int M, int N, int K, int t, typename Tr<T>::R
 //   zero(m, n, a, lda)
 //   bcast_row(root_col, p, count) / bcast_col(root_row, p, count)      in place, count elements of T
 //   reduce_row(root_col, p, count) / reduce_col(root_row, p, count)    sum, in place; only the root's buffer is defined after
+//   group_begin() / group_end()                                        collectives in between may be launched together
 template <class T, class Ops>
 int triangular_solve_dist(Ops& ops, const TriDistDesc& d, T alpha, const T* A, long long lda, T* B, long long ldb,
                           const TriDistWork<T>& w) {

@@ -473,6 +473,8 @@ struct DistHostOps : HostOps<T> {
         p[x] = nan_value<T>();
     return bad ? 9201 : 0;
   }
+  int group_begin() { return 0; }  // the shared-memory collectives complete one by one; grouping changes nothing here
+  int group_end() { return 0; }
   int bcast_row(int root, T* p, size_t count) { return bcast(row, me_row, root, p, count); }
   int bcast_col(int root, T* p, size_t count) { return bcast(col, me_col, root, p, count); }
   int reduce_row(int root, T* p, size_t count) { return reduce(row, me_row, root, p, count); }
