@@ -47,7 +47,7 @@ oracle:
 # CPU execution of the triangular solver's algorithm template and kernel bodies (test infrastructure only)
 emu: tests/emu/_build/libsolver_emu.so
 
-tests/emu/_build/libsolver_emu.so: tests/emu/solver_emu.cu $(SRC)/triangular_solver.h $(SRC)/gen_to_std.h $(SRC)/triangular_solver_dist.h $(SRC)/gen_to_std_dist.h $(SRC)/schedule.h $(CSRC)/solver_kernels.cuh $(CSRC)/common.cuh
+tests/emu/_build/libsolver_emu.so: tests/emu/solver_emu.cu $(SRC)/triangular_solver.h $(SRC)/gen_to_std.h $(SRC)/triangular_solver_dist.h $(SRC)/gen_to_std_dist.h $(SRC)/redistribute.h $(CSRC)/copy_rects.cuh $(SRC)/schedule.h $(CSRC)/solver_kernels.cuh $(CSRC)/common.cuh
 	@mkdir -p tests/emu/_build
 	$(NVCC) -O2 -std=c++17 -Wno-deprecated-gpu-targets -shared -Xcompiler -fPIC,-pthread -I$(CSRC) -I$(SRC) -o $@ $<
 

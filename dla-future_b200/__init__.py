@@ -84,8 +84,8 @@ def lib():
 
 
 from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
-from ._engine_api import (CholeskyPlan, GenToStdDistPlan, GenToStdPlan, Grid, StepInfo, TriangularSolverDistPlan,  # noqa: E402,F401
-                          TriangularSolverPlan, schedule_step)
+from ._engine_api import (CholeskyPlan, GenToStdDistPlan, GenToStdPlan, Grid, RedistributePlan,  # noqa: E402,F401
+                          StepInfo, TriangularSolverDistPlan, TriangularSolverPlan, schedule_step)
 
 
 def check(err, what=""):

@@ -1,4 +1,4 @@
-"""ctypes signatures of include/dlafb_engine.h, include/dlafb_solver.h and include/dlafb_gen_to_std.h plus thin Python
+"""ctypes signatures of include/dlafb_engine.h, include/dlafb_solver.h, include/dlafb_gen_to_std.h and include/dlafb_matrix.h plus thin Python
 wrappers (Grid, CholeskyPlan, TriangularSolverPlan, GenToStdPlan) used by the tests and by bench.py. No arithmetic
 happens here."""
 import ctypes
@@ -70,6 +70,12 @@ ENGINE_API = {
     "dlafb_gen_to_std_dist_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_gen_to_std_dist_plan_workspace_bytes": (ctypes.c_size_t, [c_vp]),
     "dlafb_gen_to_std_dist_plan_destroy": (c_int, [c_vp]),
+    # include/dlafb_matrix.h
+    "dlafb_redistribute_plan_create": (c_int, [ctypes.POINTER(c_vp), c_vp, c_char, c_i64, c_i64, c_i64, c_i64, c_int,
+                                               c_int, c_i64, c_i64, c_int, c_int]),
+    "dlafb_redistribute_plan_local_sizes": (c_int, [c_vp, P_i64, P_i64, P_i64, P_i64]),
+    "dlafb_redistribute_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
+    "dlafb_redistribute_plan_destroy": (c_int, [c_vp]),
 }
 
 
@@ -280,4 +286,26 @@ class GenToStdDistPlan:
     def close(self):
         if self.h:
             self.L.dlafb_gen_to_std_dist_plan_destroy(self.h)
+            self.h = c_vp()
+
+
+class RedistributePlan:
+    """matrix::copy(src, dst, grid) (include/dlafb_matrix.h): dst <- src between two block-cyclic layouts. Collective."""
+
+    def __init__(self, L, grid, type_, m, n, src_tile, src_rank, dst_tile, dst_rank):
+        self.L = L
+        self.h = c_vp()
+        _ck(L.dlafb_redistribute_plan_create(ctypes.byref(self.h), grid.h, type_.encode(), m, n, src_tile[0], src_tile[1],
+                                             src_rank[0], src_rank[1], dst_tile[0], dst_tile[1], dst_rank[0],
+                                             dst_rank[1]), "redistribute_plan_create")
+        v = [c_i64() for _ in range(4)]
+        _ck(L.dlafb_redistribute_plan_local_sizes(self.h, *v), "redistribute_plan_local_sizes")
+        self.src_rows, self.src_cols, self.dst_rows, self.dst_cols = (x.value for x in v)
+
+    def run(self, src_ptr, ld_src, dst_ptr, ld_dst, stream):
+        _ck(self.L.dlafb_redistribute_plan_run(self.h, src_ptr, ld_src, dst_ptr, ld_dst, stream), "redistribute_plan_run")
+
+    def close(self):
+        if self.h:
+            self.L.dlafb_redistribute_plan_destroy(self.h)
             self.h = c_vp()

@@ -2,6 +2,7 @@
 // the CPU test-suite (tests/test_cxx_headers.py) catches a header that no longer compiles. Never run.
 #include "dlaf/eigensolver/gen_to_std.h"
 #include "dlaf/factorization/cholesky.h"
+#include "dlaf/matrix/copy.h"
 #include "dlaf/solver/triangular.h"
 
 #include <complex>
@@ -19,6 +20,10 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
                                                   blas::Diag::Unit, T(1), a, b);
   eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, b, a);
   eigensolver::internal::generalized_to_standard<Backend::GPU, Device::GPU, T>(grid, blas::Uplo::Upper, b, a);
+  Matrix<T, Device::GPU> c(GlobalElementSize(8, 8), TileElementSize(2, 2), grid);
+  Matrix<T, Device::GPU> d(GlobalElementSize(8, 8), TileElementSize(4, 4), grid);
+  matrix::copy(c, d, grid);
+  d.waitLocalTiles();
   a.waitLocalTiles();
   b.waitLocalTiles();
 }

@@ -22,6 +22,7 @@
 #include <thread>
 
 #include "gen_to_std.h"
+#include "redistribute.h"
 #include "gen_to_std_dist.h"
 #include "triangular_solver.h"
 #include "triangular_solver_dist.h"
@@ -571,6 +572,82 @@ int gen_to_std_dist_emu(int P, int Q, int src_r, int src_c, char uplo, int n, in
   return 0;
 }
 
+// ---- redistribution for all the ranks of a simulated grid: the product's list builder and kernel body, the
+// all-to-all through shared memory (every rank reads its segments straight out of the senders' buffers)
+struct SimWorld {
+  SimComm comm;
+  std::vector<const void*> sendbuf;
+  std::vector<const RedistLists*> lists;
+};
+
+template <class T>
+struct RedistHostOps {
+  const RedistLists* L;
+  SimWorld* world;
+  int me;
+  int copy_rects(int which, const T* src, T* dst) {
+    const std::vector<CopyRect>& v = which == 0 ? L->pack : which == 1 ? L->self : L->unpack;
+    for (int b = 0; b < (int)v.size(); ++b)
+      for (int th = 0; th < kCopyRectThreads; ++th)
+        copy_rects_body<T>(v.data(), src, dst, b, th, kCopyRectThreads);
+    return 0;
+  }
+  int alltoallv(const T* sendbuf, T* recvbuf) {
+    world->sendbuf[me] = sendbuf;
+    world->lists[me] = L;
+    world->comm.barrier();
+    int bad = 0;
+    for (int r = 0; r < world->comm.size; ++r) {
+      if (r == me)
+        continue;
+      const RedistLists* theirs = world->lists[r];
+      if (theirs->send_cnt[me] != L->recv_cnt[r]) {  // NCCL would hang or corrupt on a size mismatch
+        ++bad;
+        continue;
+      }
+      if (L->recv_cnt[r] > 0)
+        std::memcpy(recvbuf + L->recv_off[r], static_cast<const T*>(world->sendbuf[r]) + theirs->send_off[me],
+                    (size_t)L->recv_cnt[r] * sizeof(T));
+    }
+    world->comm.barrier();
+    return bad ? 9400 : 0;
+  }
+};
+
+template <class T>
+int redistribute_emu(int P, int Q, char ordering, long long m, long long n, int mb_s, int nb_s, int sr_s, int sc_s, int mb_d,
+                     int nb_d, int sr_d, int sc_d, void* const* src, const long long* ld_src, void* const* dst,
+                     const long long* ld_dst) {
+  SimWorld world;
+  world.comm.size = P * Q;
+  world.sendbuf.assign(P * Q, nullptr);
+  world.lists.assign(P * Q, nullptr);
+  std::vector<int> err(P * Q, 0);
+  std::vector<std::thread> th;
+  for (int pr = 0; pr < P; ++pr)
+    for (int pc = 0; pc < Q; ++pc)
+      th.emplace_back([&, pr, pc] {
+        RedistDesc d{m, n, mb_s, nb_s, sr_s, sc_s, mb_d, nb_d, sr_d, sc_d, P, Q, pr, pc, ordering};
+        const int r = redist_linear_rank(d, pr, pc);
+        if (!redist_valid(d)) {
+          err[r] = 9401;
+          return;
+        }
+        const RedistLists L = redist_build(d, ld_src[r], ld_dst[r]);
+        Guarded<T> sb((size_t)L.send_total), rb((size_t)L.recv_total);
+        RedistHostOps<T> ops{&L, &world, r};
+        err[r] = redistribute<T>(ops, L, static_cast<const T*>(src[r]), static_cast<T*>(dst[r]), sb.data(), rb.data());
+        if (err[r] == 0 && !(sb.intact() && rb.intact()))
+          err[r] = 9300;
+      });
+  for (auto& t : th)
+    t.join();
+  for (int e : err)
+    if (e)
+      return e;
+  return 0;
+}
+
 }  // namespace
 
 #define EMU_TYPED(X, T)                                                                                             \
@@ -588,6 +665,12 @@ int gen_to_std_dist_emu(int P, int Q, int src_r, int src_c, char uplo, int n, in
   }                                                                                                                 \
   int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
     return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
+  }                                                                                                                 \
+  int emu_redistribute_##X(int P, int Q, char ordering, long long m, long long n, int mb_s, int nb_s, int sr_s,     \
+                           int sc_s, int mb_d, int nb_d, int sr_d, int sc_d, void* const* src,                      \
+                           const long long* ld_src, void* const* dst, const long long* ld_dst) {                    \
+    return redistribute_emu<T>(P, Q, ordering, m, n, mb_s, nb_s, sr_s, sc_s, mb_d, nb_d, sr_d, sc_d, src, ld_src,   \
+                               dst, ld_dst);                                                                        \
   }                                                                                                                 \
   int emu_gen_to_std_dist_##X(int P, int Q, int src_r, int src_c, char uplo, int n, int nb, void* const* a,         \
                               const long long* lda, void* const* f, const long long* ldf) {                          \

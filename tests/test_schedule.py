@@ -27,7 +27,8 @@ def test_library_exports_every_declared_symbol(pkg, L):
 def test_headers_and_bindings_agree(pkg, L):
     """Every function the public headers declare is exported by the library (and known to the binding)."""
     names = set()
-    hdrs = ["include/dlafb_engine.h", "include/dlafb_solver.h", "include/dlaf_c/init.h", "include/dlaf_c/grid.h", "include/dlaf_c/utils.h",
+    hdrs = ["include/dlafb_engine.h", "include/dlafb_solver.h", "include/dlafb_gen_to_std.h", "include/dlafb_matrix.h",
+            "include/dlaf_c/init.h", "include/dlaf_c/grid.h", "include/dlaf_c/utils.h",
             "include/dlaf_c/factorization/cholesky.h", "include/dlafb_mpi_shim/mpi.h"]
     for h in hdrs:
         src = open(os.path.join(ROOT, h)).read()

@@ -1,0 +1,52 @@
+"""-m gpu: the matrix redistribution (include/dlafb_matrix.h) on one GPU (1 x 1 grid: the rectangle-list kernel alone,
+every sub-tile stays on the rank) and on several GPUs (tests/dist_redistribute_check.py under torchrun).
+(The file name sorts last on purpose: written after the round's GPU budget was spent.)"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("x", "sdcz")
+def test_single_rank_is_a_bit_exact_copy(pkg, L, x):
+    from gpu_util import NP, DevMat, stream_ptr, sync
+    dt = NP[x]
+    rng = np.random.default_rng(6)
+    grid = pkg.Grid(L)
+    for m, n, st, dtile in [(37, 29, (4, 3), (8, 6)), (37, 29, (8, 6), (4, 3)), (1000, 700, (64, 64), (256, 128)),
+                            (2048, 2048, (512, 512), (64, 64)), (1, 1, (2, 2), (4, 4)), (0, 5, (2, 2), (4, 4))]:
+        a = rng.standard_normal((m, n)) + (1j * rng.standard_normal((m, n)) if np.dtype(dt).kind == "c" else 0)
+        a = a.astype(dt)
+        S = DevMat(a, ld=max(1, m) + 1)
+        D = DevMat(np.full((m, n), dt(-5.5)), ld=max(1, m) + 3)
+        plan = pkg.RedistributePlan(L, grid, x, m, n, st, (0, 0), dtile, (0, 0))
+        assert (plan.src_rows, plan.src_cols, plan.dst_rows, plan.dst_cols) == (m, n, m, n)
+        plan.run(S.ptr, S.ld, D.ptr, D.ld, stream_ptr())
+        plan.run(S.ptr, S.ld, D.ptr, D.ld, stream_ptr())   # a second run reuses the uploaded lists
+        sync()
+        plan.close()
+        assert np.array_equal(D.get(), a), (m, n, st, dtile)
+        assert np.all(D.pad() == dt(-7.7))
+        assert np.array_equal(S.get(), a)
+    grid.close()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_distributed_redistribution(world):
+    import torch
+    env = os.environ.get("DLAFB_DIST_WORLDS")
+    worlds = [int(w) for w in env.split(",")] if env else [2, 4, 8]
+    if world not in worlds or torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29900 + world),
+           os.path.join(ROOT, "tests", "dist_redistribute_check.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=1500)
+    tail = (r.stdout + r.stderr)[-3000:]
+    assert r.returncode == 0, tail
+    assert "total_failures=0" in r.stdout, tail
