@@ -16,6 +16,7 @@
 #include <unordered_map>
 
 #include "../../include/dlafb_engine.h"
+#include "../../include/dlafb_matrix.h"
 #include "../../include/dlafb_mpi_shim/mpi.h"
 #include "grid.h"
 
@@ -77,6 +78,86 @@ void drop_plans_of(int ctx) {
 
 size_t elem_size(char t) { return t == 's' ? 4 : (t == 'z' ? 16 : 8); }
 
+// Callers that come from ScaLAPACK bring block sizes of 32 - 128; the factorization wants 512 (the contraction's K and
+// the number of dependent steps). With DLAFB_POTRF_REDISTRIBUTE=1 a matrix with a small block size is redistributed on
+// the device to the largest block size <= 512 that is a multiple of both the caller's block size and 16, factorized
+// there and redistributed back (matrix::copy(src, dst, grid), include/dlaf/matrix/copy.h:118-231 of the reference, is
+// the same tool; the reference's C API does not use it for this call). Off by default until it has been timed.
+int redistribution_block(int n, int nb_in) {
+  const char* e = getenv("DLAFB_POTRF_REDISTRIBUTE");
+  if (!e || e[0] != '1' || nb_in >= 256 || n < 2048)
+    return 0;
+  int l = nb_in;
+  while (l % 16 != 0)
+    l += nb_in;  // lcm(nb_in, 16)
+  return l <= 512 ? (512 / l) * l : 0;
+}
+
+#define CAPI_CUDA(call, what)            \
+  do {                                   \
+    const cudaError_t ce_ = (call);      \
+    if (ce_ != cudaSuccess)              \
+      die(what, (int)ce_);               \
+  } while (0)
+
+int cholesky_redistributed(dlafb_grid_t grid, char type, char uplo, void* a, int n, int nb_in, int isrc, int jsrc,
+                           int64_t ld, int nb_to) {
+  const size_t es = elem_size(type);
+  const int64_t rows_in = dlafb_dist_local_size(n, nb_in, grid->P, grid->pr, isrc);
+  const int64_t cols_in = dlafb_dist_local_size(n, nb_in, grid->Q, grid->pc, jsrc);
+  const int64_t rows_w = dlafb_dist_local_size(n, nb_to, grid->P, grid->pr, 0);
+  const int64_t cols_w = dlafb_dist_local_size(n, nb_to, grid->Q, grid->pc, 0);
+  if (rows_in > 0 && ld < rows_in)
+    die("leading dimension smaller than the local number of rows", (int)ld);
+  cudaStream_t s;
+  CAPI_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "stream creation failed");
+  cudaPointerAttributes attr{};
+  const bool on_device = (a != nullptr) && cudaPointerGetAttributes(&attr, a) == cudaSuccess &&
+                         (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+  cudaGetLastError();
+  void* in_dev = a;
+  int64_t ld_in = ld;
+  const bool have_block = rows_in > 0 && cols_in > 0;
+  if (!on_device) {
+    ld_in = ((rows_in > 0 ? rows_in : 1) + 63) / 64 * 64;
+    CAPI_CUDA(cudaMalloc(&in_dev, (size_t)ld_in * (size_t)(cols_in > 0 ? cols_in : 1) * es), "device allocation failed");
+    if (have_block)
+      CAPI_CUDA(cudaMemcpy2DAsync(in_dev, ld_in * es, a, ld * es, rows_in * es, cols_in, cudaMemcpyHostToDevice, s),
+                "upload failed");
+  }
+  const int64_t ldw = ((rows_w > 0 ? rows_w : 1) + 63) / 64 * 64;
+  void* work = nullptr;
+  CAPI_CUDA(cudaMalloc(&work, (size_t)ldw * (size_t)(cols_w > 0 ? cols_w : 1) * es), "device allocation failed");
+  dlafb_redistribute_plan_t fwd = nullptr, bwd = nullptr;
+  dlafb_chol_plan_t plan = nullptr;
+  int e;
+  if ((e = dlafb_redistribute_plan_create(&fwd, grid, type, n, n, nb_in, nb_in, isrc, jsrc, nb_to, nb_to, 0, 0)) != 0 ||
+      (e = dlafb_redistribute_plan_create(&bwd, grid, type, n, n, nb_to, nb_to, 0, 0, nb_in, nb_in, isrc, jsrc)) != 0 ||
+      (e = dlafb_cholesky_plan_create(&plan, grid, type, uplo, n, nb_to, 0, 0)) != 0)
+    die("plan creation failed", e);
+  if ((e = dlafb_redistribute_plan_run(fwd, in_dev, ld_in, work, ldw, s)) != 0)
+    die("redistribution failed", e);
+  if ((e = dlafb_cholesky_plan_run(plan, work, ldw, s)) != 0)
+    die("factorization failed to launch", e);
+  int info = 0;
+  if ((e = dlafb_cholesky_plan_info(plan, &info)) != 0)
+    die("factorization failed", e);
+  if ((e = dlafb_redistribute_plan_run(bwd, work, ldw, in_dev, ld_in, s)) != 0)
+    die("redistribution failed", e);
+  if (!on_device && have_block)
+    CAPI_CUDA(cudaMemcpy2DAsync(a, ld * es, in_dev, ld_in * es, rows_in * es, cols_in, cudaMemcpyDeviceToHost, s),
+              "download failed");
+  CAPI_CUDA(cudaStreamSynchronize(s), "stream synchronisation failed");
+  dlafb_redistribute_plan_destroy(fwd);
+  dlafb_redistribute_plan_destroy(bwd);
+  dlafb_cholesky_plan_destroy(plan);
+  cudaFree(work);
+  if (!on_device)
+    cudaFree(in_dev);
+  cudaStreamDestroy(s);
+  return info;
+}
+
 int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   if (!g_initialized)
     die("dlaf_cholesky_factorization called before dlaf_initialize", -1);
@@ -105,6 +186,8 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   const PlanKey key{ctx, type, uplo == 'u' ? 'U' : (uplo == 'l' ? 'L' : uplo), d.n, d.nb, sub_isrc, sub_jsrc};
   if (key.uplo != 'L' && key.uplo != 'U')
     die("uplo must be 'L' or 'U'", -1);
+  if (const int nb_to = redistribution_block(d.n, d.nb))
+    return cholesky_redistributed(grid, type, key.uplo, a, d.n, d.nb, sub_isrc, sub_jsrc, d.ld, nb_to);
   PlanEntry& pe = g_plans[key];
   int e;
   if (!pe.plan) {

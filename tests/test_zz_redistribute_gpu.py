@@ -50,3 +50,43 @@ def test_distributed_redistribution(world):
     tail = (r.stdout + r.stderr)[-3000:]
     assert r.returncode == 0, tail
     assert "total_failures=0" in r.stdout, tail
+
+
+@pytest.mark.parametrize("x,n,nb", [("d", 2304, 64), ("d", 2100, 48), ("z", 2048, 32), ("s", 2048, 128)])
+@pytest.mark.parametrize("uplo", "LU")
+def test_pxpotrf_with_redistribution_to_large_blocks(pkg, L, monkeypatch, x, n, nb, uplo):
+    """DLAFB_POTRF_REDISTRIBUTE=1: a caller with ScaLAPACK-sized blocks gets redistribute -> Cholesky at <= 512 ->
+    redistribute back inside dlaf_p?potrf; the result must be what the plain path gives (same tolerance to the oracle),
+    and everything outside the referenced triangle must come back untouched."""
+    import ctypes
+
+    import dlaf_oracle as orc
+    from gpu_util import NP
+    dt = NP[x]
+    ctx = 47
+    L.dlaf_initialize(0, None, 0, None)
+    pkg.check(L.dlafb_mpi_init(0, 1, None), "mpi_init")
+    L.dlaf_create_grid_from_blacs_info(ctx, L.dlafb_mpi_comm_world(), 1, 1, b"R")
+    try:
+        a = orc.gen_hpd(n, nb, dt)
+        ref = a.copy(order="F")
+        assert orc.cholesky_local(uplo, ref, nb) == 0
+        keep = (np.tril if uplo == "L" else np.triu)(np.ones((n, n))) > 0
+        a_in = np.where(keep, a, dt(-9.9))
+        tol = 50 * n * float(np.finfo(dt).eps) * np.sqrt(2.0)
+        for flag in ("1", "0"):
+            monkeypatch.setenv("DLAFB_POTRF_REDISTRIBUTE", flag)
+            ld = n + 5
+            h = np.full((n, ld), dt(-7.7))
+            h[:, :n] = a_in.T
+            desca = pkg.DESC9(1, ctx, n, n, nb, nb, 0, 0, ld)
+            info = ctypes.c_int(-1)
+            getattr(L, f"dlaf_p{x}potrf")(uplo.encode(), n, h.ctypes.data, 1, 1, desca, ctypes.byref(info))
+            assert info.value == 0, flag
+            got = np.ascontiguousarray(h[:, :n].T)
+            assert np.abs(got[keep] - ref[keep]).max() <= tol * max(1.0, np.abs(ref[keep]).max()), flag
+            assert np.all(got[~keep] == dt(-9.9)), flag
+            assert np.all(h[:, n:] == dt(-7.7)), flag
+    finally:
+        L.dlaf_free_grid(ctx)
+        L.dlaf_finalize()
