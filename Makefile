@@ -45,7 +45,11 @@ oracle:
 	g++ -O2 -fopenmp -shared -fPIC -o oracle/_build/liboracle.so oracle/chol_oracle.cpp -ldl
 
 # CPU execution of the triangular solver's algorithm template and kernel bodies (test infrastructure only)
-emu: tests/emu/_build/libsolver_emu.so
+emu: tests/emu/_build/libsolver_emu.so tests/emu/_build/libsimt_wide_emu.so
+
+tests/emu/_build/libsimt_wide_emu.so: tests/emu/simt_wide_emu.cu $(CSRC)/gemm_simt_wide.cuh $(CSRC)/gemm_simt.cuh $(CSRC)/common.cuh
+	@mkdir -p tests/emu/_build
+	$(NVCC) -O1 -std=c++17 -Wno-deprecated-gpu-targets -diag-suppress 20014 -shared -Xcompiler -fPIC,-pthread,-ffp-contract=off -I$(CSRC) -o $@ $<
 
 tests/emu/_build/libsolver_emu.so: tests/emu/solver_emu.cu $(SRC)/triangular_solver.h $(SRC)/gen_to_std.h $(SRC)/triangular_solver_dist.h $(SRC)/gen_to_std_dist.h $(SRC)/redistribute.h $(CSRC)/copy_rects.cuh $(SRC)/schedule.h $(CSRC)/solver_kernels.cuh $(CSRC)/common.cuh
 	@mkdir -p tests/emu/_build

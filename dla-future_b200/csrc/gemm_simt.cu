@@ -1,8 +1,67 @@
 // Generic register-tiled contraction kernel (see gemm_simt.cuh).
 #include "gemm_simt.cuh"
 
+#include <cstdlib>
+#include <type_traits>
+
+#include "gemm_simt_wide.cuh"
+
 namespace dlafb {
 namespace {
+
+// ---- wide float variant (gemm_simt_wide.cuh) ----
+struct WideDeviceCtx {
+  float* sm;
+  __device__ int tid() const { return threadIdx.x; }
+  __device__ int bx() const { return blockIdx.x; }
+  __device__ int by() const { return blockIdx.y; }
+  __device__ float* smem() const { return sm; }
+  __device__ void sync() const { __syncthreads(); }
+};
+
+__global__ void __launch_bounds__(kWideThreads, 2) gemm_simt_wide_kernel(const SimtParams<float> p) {
+  __shared__ __align__(16) float sm[kWideSmemFloats];
+  WideDeviceCtx c{sm};
+  gemm_simt_wide_body(p, c);
+}
+
+// DLAFB_SGEMM_WIDE=1 routes float contractions to the 128 x 128 kernel (read once).
+bool wide_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DLAFB_SGEMM_WIDE");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+
+template <class T>
+bool launch_wide(cudaStream_t, const SimtParams<T>&, unsigned, unsigned, cudaError_t*) {
+  return false;
+}
+template <>
+bool launch_wide<float>(cudaStream_t stream, const SimtParams<float>& p, unsigned nblocks_x, unsigned nblocks_y,
+                        cudaError_t* err) {
+  if (!wide_enabled())
+    return false;
+  // the callers count 64 x 64 blocks: RECT mode ceil(M / 64) x ceil(N / 64); LIST mode items * sub^2, sub = ceil(tile / 64)
+  unsigned nx, ny;
+  if (p.list != nullptr) {
+    if (p.sub <= 0)
+      return false;
+    const unsigned items = nblocks_x / (unsigned)(p.sub * p.sub);
+    const unsigned sub = (unsigned)((p.tile + kWideTile - 1) / kWideTile);
+    nx = items * sub * sub;
+    ny = 1;
+  }
+  else {
+    nx = (nblocks_x + 1) / 2;
+    ny = (nblocks_y + 1) / 2;
+  }
+  gemm_simt_wide_kernel<<<dim3(nx, ny), kWideThreads, 0, stream>>>(p);
+  ++g_launches;
+  *err = cudaGetLastError();
+  return true;
+}
 
 constexpr int kSK = 8;  // K-slice
 
@@ -122,6 +181,9 @@ template <class T>
 cudaError_t launch_gemm_simt(cudaStream_t stream, const SimtParams<T>& p, unsigned nblocks_x, unsigned nblocks_y) {
   if (nblocks_x == 0 || nblocks_y == 0)
     return cudaSuccess;
+  cudaError_t werr = cudaSuccess;
+  if (launch_wide<T>(stream, p, nblocks_x, nblocks_y, &werr))
+    return werr;
   gemm_simt_kernel<T><<<dim3(nblocks_x, nblocks_y), 256, 0, stream>>>(p);
   ++g_launches;
   return cudaGetLastError();
