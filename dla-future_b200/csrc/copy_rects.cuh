@@ -33,14 +33,37 @@ __host__ __device__ inline void copy_rects_body(const CopyRect* __restrict__ rec
   long long col = thread / r.rows;
   const int drow = nthreads % r.rows;
   const long long dcol = nthreads / r.rows;
-  for (long long idx = thread; idx < total; idx += nthreads) {
-    d[row + col * r.dst_ld] = s[row + col * r.src_ld];
+  auto advance = [&]() {
     row += drow;
     col += dcol;
     if (row >= r.rows) {
       row -= r.rows;
       ++col;
     }
+  };
+  long long idx = thread;
+  // four independent loads in flight per thread before the first store (a 64 x 64 double rectangle is 16 elements per
+  // thread: one load at a time would leave the copy latency bound)
+  while (idx + 3LL * nthreads < total) {
+    const long long o0s = row + col * r.src_ld, o0d = row + col * r.dst_ld;
+    advance();
+    const long long o1s = row + col * r.src_ld, o1d = row + col * r.dst_ld;
+    advance();
+    const long long o2s = row + col * r.src_ld, o2d = row + col * r.dst_ld;
+    advance();
+    const long long o3s = row + col * r.src_ld, o3d = row + col * r.dst_ld;
+    advance();
+    const T v0 = s[o0s], v1 = s[o1s], v2 = s[o2s], v3 = s[o3s];
+    d[o0d] = v0;
+    d[o1d] = v1;
+    d[o2d] = v2;
+    d[o3d] = v3;
+    idx += 4LL * nthreads;
+  }
+  while (idx < total) {
+    d[row + col * r.dst_ld] = s[row + col * r.src_ld];
+    advance();
+    idx += nthreads;
   }
 }
 
