@@ -16,7 +16,10 @@ from test_redistribute_emu import linear, redistribute
 from test_triangular_dist_emu import emu as tri_emu_fixture  # noqa: F401
 from test_triangular_dist_emu import run as tri_run
 
-COMMON = dict(deadline=None, max_examples=60, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+import os
+
+N_EXAMPLES = int(os.environ.get("DLAFB_PROPERTY_EXAMPLES", "60"))   # raise for a deeper run
+COMMON = dict(deadline=None, max_examples=N_EXAMPLES, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
 grids = st.tuples(st.integers(1, 4), st.integers(1, 4)).filter(lambda g: g[0] * g[1] <= 8)
 
 
@@ -74,7 +77,7 @@ def test_distributed_solve_satisfies_the_equation(tri_emu_fixture, grid, side, u
     assert np.abs(lhs - alpha * b).max() <= 1e-12 * scale * np.linalg.cond(opa)
 
 
-@settings(**{**COMMON, "max_examples": 40})
+@settings(**{**COMMON, "max_examples": max(1, 2 * N_EXAMPLES // 3)})
 @given(grid=grids, uplo=st.sampled_from("LU"), n=st.integers(1, 36), nb=st.integers(1, 9), x=st.sampled_from("dz"),
        seed=st.integers(0, 10 ** 6))
 def test_distributed_reduction_matches_the_dense_formula(g2s_emu_fixture, grid, uplo, n, nb, x, seed):  # noqa: F811
