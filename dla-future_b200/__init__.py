@@ -85,7 +85,7 @@ def lib():
 
 from ._c_api import DESC9, DLAFDescriptor  # noqa: E402,F401
 from ._engine_api import (CholeskyPlan, GenToStdDistPlan, GenToStdPlan, Grid, RedistributePlan,  # noqa: E402,F401
-                          StepInfo, TriangularSolverDistPlan, TriangularSolverPlan, schedule_step)
+                          StepInfo, TriangularSolverDistPlan, TriangularSolverPlan, max_norm, schedule_step)
 
 
 def check(err, what=""):

@@ -76,6 +76,7 @@ ENGINE_API = {
     "dlafb_redistribute_plan_local_sizes": (c_int, [c_vp, P_i64, P_i64, P_i64, P_i64]),
     "dlafb_redistribute_plan_run": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp]),
     "dlafb_redistribute_plan_destroy": (c_int, [c_vp]),
+    "dlafb_max_norm": (c_int, [c_vp, c_char, c_char, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_vp, c_i64, c_vp, P_dbl]),
 }
 
 
@@ -309,3 +310,11 @@ class RedistributePlan:
         if self.h:
             self.L.dlafb_redistribute_plan_destroy(self.h)
             self.h = c_vp()
+
+
+def max_norm(L, grid, type_, uplo, m, n, mb, nb, src, a_ptr, lda, stream):
+    """dlaf::auxiliary::max_norm over the grid (include/dlafb_matrix.h). Collective; every rank gets the value."""
+    out = ctypes.c_double()
+    _ck(L.dlafb_max_norm(grid.h, type_.encode(), uplo.encode(), m, n, mb, nb, src[0], src[1], a_ptr, lda, stream,
+                         ctypes.byref(out)), "max_norm")
+    return out.value

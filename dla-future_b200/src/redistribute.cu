@@ -6,8 +6,10 @@
 
 #include <new>
 
+#include "dlafb_engine.h"
 #include "dlafb_matrix.h"
 #include "grid.h"
+#include "tile_ops.cuh"
 
 namespace dlafb {
 namespace {
@@ -116,6 +118,37 @@ int run_typed(RedistPlan& p, const void* src, void* dst, cudaStream_t s) {
                          static_cast<T*>(p.recvbuf));
 }
 
+// max |a_ij| over this rank's part of the (global) uplo region: for 'L' the tiles strictly below the global diagonal in
+// full and the diagonal tiles' lower triangles - per local column tile one launch for the rows below and one for a
+// local diagonal tile (auxiliary/norm/mc.h:35-95 walks the same tiles one task per tile).
+template <class T>
+int local_max_abs(cudaStream_t s, char uplo, int64_t m, int64_t n, int64_t mb, int64_t nb, const dlafb_grid* g, int src_r,
+                  int src_c, const void* a, int64_t lda, double* dev_out) {
+  const Dist1D R{m, mb, g->P, g->pr, src_r}, C{n, nb, g->Q, g->pc, src_c};
+  const int64_t lrows = R.local_size(), lcols = C.local_size();
+  const T* A = static_cast<const T*>(a);
+  if (lrows <= 0 || lcols <= 0)
+    return 0;
+  if (uplo == 'G')
+    return (int)max_abs<T>(s, 'G', (int)lrows, (int)lcols, A, lda, dev_out);
+  for (int64_t jl = 0; jl < C.nloc_tiles(); ++jl) {
+    const int64_t j = C.global_of(jl);
+    const int wj = (int)C.tile_size(j);
+    int64_t below = R.next_local(j) * mb;
+    const T* cj = A + jl * nb * lda;
+    cudaError_t e;
+    if (R.owner(j) == g->pr && below < lrows) {
+      const int hj = (int)R.tile_size(j);
+      if ((e = max_abs<T>(s, 'L', hj, wj, cj + below, lda, dev_out)) != cudaSuccess)
+        return (int)e;
+      below += mb;
+    }
+    if (below < lrows && (e = max_abs<T>(s, 'G', (int)(lrows - below), wj, cj + below, lda, dev_out)) != cudaSuccess)
+      return (int)e;
+  }
+  return 0;
+}
+
 }  // namespace
 }  // namespace dlafb
 
@@ -181,6 +214,42 @@ int dlafb_redistribute_plan_run(dlafb_redistribute_plan_t plan, const void* src,
 
 int dlafb_redistribute_plan_destroy(dlafb_redistribute_plan_t plan) {
   delete reinterpret_cast<RedistPlan*>(plan);
+  return 0;
+}
+
+int dlafb_max_norm(dlafb_grid_t grid, char type, char uplo, int64_t m, int64_t n, int64_t mb, int64_t nb, int src_r,
+                   int src_c, const void* a, int64_t lda, void* stream, double* result) {
+  if (!grid || !result || (type != 's' && type != 'd' && type != 'c' && type != 'z') || (uplo != 'L' && uplo != 'G') ||
+      m < 0 || n < 0 || mb < 1 || nb < 1 || src_r < 0 || src_r >= grid->P || src_c < 0 || src_c >= grid->Q ||
+      (uplo == 'L' && (m != n || mb != nb)))
+    return -1;
+  *result = 0.0;  // LAPACK: the norm of an empty matrix is 0 (auxiliary/norm.h:41-43)
+  if (m == 0 || n == 0)
+    return 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  double* dev = nullptr;
+  cudaError_t ce = cudaMalloc(&dev, sizeof(double));
+  if (ce != cudaSuccess)
+    return (int)ce;
+  cudaMemsetAsync(dev, 0, sizeof(double), s);
+  int e;
+  switch (type) {
+    case 's': e = local_max_abs<float>(s, uplo, m, n, mb, nb, grid, src_r, src_c, a, lda, dev); break;
+    case 'd': e = local_max_abs<double>(s, uplo, m, n, mb, nb, grid, src_r, src_c, a, lda, dev); break;
+    case 'c': e = local_max_abs<float2>(s, uplo, m, n, mb, nb, grid, src_r, src_c, a, lda, dev); break;
+    default: e = local_max_abs<double2>(s, uplo, m, n, mb, nb, grid, src_r, src_c, a, lda, dev); break;
+  }
+  double local = 0.0;
+  if (e == 0)
+    e = (int)cudaMemcpyAsync(&local, dev, sizeof(double), cudaMemcpyDeviceToHost, s);
+  if (e == 0)
+    e = (int)cudaStreamSynchronize(s);
+  cudaFree(dev);
+  if (e != 0)
+    return e;
+  if ((e = dlafb_grid_allreduce_max(grid, &local)) != 0)
+    return e;
+  *result = local;
   return 0;
 }
 

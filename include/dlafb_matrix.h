@@ -41,6 +41,14 @@ int dlafb_redistribute_plan_run(dlafb_redistribute_plan_t plan, const void* src,
 /* The caller synchronises with the last run first. */
 int dlafb_redistribute_plan_destroy(dlafb_redistribute_plan_t plan);
 
+/* Max norm of a distributed matrix, max |a_ij| over the general matrix (uplo 'G', any m x n with mb x nb tiles) or over
+ * the lower triangle of a square matrix with square tiles (uplo 'L': valid for symmetric / Hermitian / lower-triangular
+ * data). Reference: dlaf::auxiliary::max_norm(grid, rank, uplo, A), include/dlaf/auxiliary/norm.h:35-58 - implemented
+ * there for the CPU backend only (auxiliary/norm/mc.h:35-149); 0 for an empty matrix (:41-43). Collective over the grid;
+ * synchronises; every rank gets the result (the reference delivers it to one rank). NaN entries are reported as +inf. */
+int dlafb_max_norm(dlafb_grid_t grid, char type, char uplo, int64_t m, int64_t n, int64_t mb, int64_t nb, int src_r,
+                   int src_c, const void* a, int64_t lda, void* stream, double* result);
+
 #ifdef __cplusplus
 }
 #endif

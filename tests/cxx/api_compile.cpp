@@ -1,5 +1,6 @@
 // TEST INFRASTRUCTURE: instantiates every public C++ front end of include/dlaf/ for the four element types, so that
 // the CPU test-suite (tests/test_cxx_headers.py) catches a header that no longer compiles. Never run.
+#include "dlaf/auxiliary/norm.h"
 #include "dlaf/eigensolver/gen_to_std.h"
 #include "dlaf/factorization/cholesky.h"
 #include "dlaf/matrix/copy.h"
@@ -24,6 +25,7 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
   Matrix<T, Device::GPU> d(GlobalElementSize(8, 8), TileElementSize(4, 4), grid);
   matrix::copy(c, d, grid);
   d.waitLocalTiles();
+  (void)auxiliary::max_norm<Backend::GPU, Device::GPU, T>(grid, comm::Index2D(0, 0), blas::Uplo::Lower, d);
   a.waitLocalTiles();
   b.waitLocalTiles();
 }

@@ -64,6 +64,20 @@ def main():
                         ncases += 1
                         if not ok or not np.array_equal(got, want):
                             failures.append(f"{x} {m}x{n} {st}->{dtile} src={sr} dst={dr} grid={P}x{Q}{order} ok={ok}")
+            # distributed max norm (dlafb_max_norm): Lower ignores what lies above the global diagonal
+            for x, m, nb in [("d", 301, 16), ("z", 77, 8), ("s", 5, 8)]:
+                a = rng.uniform(-1, 1, (m, m)) + (1j * rng.uniform(-1, 1, (m, m)) if x in "cz" else 0)
+                a = a.astype(NP[x])
+                a[1, m - 1] = 40.0
+                a[m - 1, 0] = -30.0
+                src = (P - 1, min(1, Q - 1))
+                la, _, _ = orc.local_block(a, nb, nb, (P, Q), me, src)
+                da, lda, _ = to_dev(la, 1, NP[x](-7.7))
+                gl = pkg.max_norm(L, grid, x, "L", m, m, nb, nb, src, da.data_ptr(), lda, stream)
+                gg = pkg.max_norm(L, grid, x, "G", m, m, nb, nb, src, da.data_ptr(), lda, stream)
+                ncases += 1
+                if abs(gl - 30.0) > 1e-5 or abs(gg - 40.0) > 1e-5:
+                    failures.append(f"max_norm {x} m={m} nb={nb} grid={P}x{Q}{order}: L={gl} G={gg}")
             if order == "R":
                 # ScaLAPACK-sized blocks in, factorization at 512, ScaLAPACK-sized blocks out
                 n, nb_in, nb = 2048, 64, 512
