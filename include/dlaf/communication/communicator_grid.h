@@ -8,6 +8,7 @@
 #include <utility>
 
 #include "dlaf/communication/communicator.h"
+#include "dlaf/communication/communicator_pipeline.h"
 #include "dlafb_engine.h"
 
 // internal hooks of libdlaf_b200 (src/c_api.cu): grid over the MPI-shim communicator
@@ -61,6 +62,12 @@ public:
   Communicator& full_communicator() noexcept { return full_; }
   common::Ordering ordering() const noexcept { return ordering_; }
   std::size_t num_pipelines() const noexcept { return npipelines_; }
+
+  /// Pipelines along the row / column / full communicator (communicator_grid.h:110-131 of the reference): see
+  /// communicator_pipeline.h for what they carry in this build.
+  CommunicatorPipeline<CommunicatorType::Row> row_communicator_pipeline() { return {grid_, rank_, size_}; }
+  CommunicatorPipeline<CommunicatorType::Col> col_communicator_pipeline() { return {grid_, rank_, size_}; }
+  CommunicatorPipeline<CommunicatorType::Full> full_communicator_pipeline() { return {grid_, rank_, size_}; }
 
   /// Grid-wide barrier on the device communicator.
   void barrier() const { dlafb_grid_barrier(grid_); }

@@ -3,6 +3,8 @@
 #pragma once
 #include <dlaf_c/init.h>
 
+#include "dlaf/tune.h"
+
 namespace dlaf {
 
 struct configuration {

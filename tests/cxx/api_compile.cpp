@@ -1,6 +1,9 @@
 // TEST INFRASTRUCTURE: instantiates every public C++ front end of include/dlaf/ for the four element types, so that
 // the CPU test-suite (tests/test_cxx_headers.py) catches a header that no longer compiles. Never run.
 #include "dlaf/auxiliary/norm.h"
+#include "dlaf/common/round_robin.h"
+#include "dlaf/common/timer.h"
+#include "dlaf/tune.h"
 #include "dlaf/eigensolver/gen_to_std.h"
 #include "dlaf/factorization/cholesky.h"
 #include "dlaf/matrix/copy.h"
@@ -30,7 +33,21 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
   b.waitLocalTiles();
 }
 
+void instantiate_misc(dlaf::comm::CommunicatorGrid& grid) {
+  auto row = grid.row_communicator_pipeline();
+  auto col = grid.col_communicator_pipeline();
+  auto full = grid.full_communicator_pipeline();
+  (void)(row.rank() + col.size() + full.rank_full_communicator(grid.rank()) + (row.valid() ? 1 : 0));
+  dlaf::common::RoundRobin<int> rr(2, 7);
+  (void)(rr.nextResource() + rr.currentResource());
+  dlaf::common::Timer<> t;
+  (void)t.elapsed();
+  dlaf::getTuneParameters().sgemm_wide = 0;
+  dlaf::getTuneParameters().apply();
+}
+
 void instantiate_all(dlaf::comm::CommunicatorGrid& grid) {
+  instantiate_misc(grid);
   instantiate<float>(grid);
   instantiate<double>(grid);
   instantiate<std::complex<float>>(grid);
