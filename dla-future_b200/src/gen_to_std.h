@@ -89,15 +89,22 @@ int gen_to_std_lower(Ops& ops, int n, int nb, T* A, long long lda, const T* L, l
       return e;
     if ((e = ops.lacpy('L', wk, wk, akk_a, lda, w.akk, w.ldk)) != 0)
       return e;
-    // A_kk <- W S W^H (S Hermitian: W S^H = W S)
+    // A_kk <- W S W^H (S Hermitian: W S^H = W S). The second product forms the stored triangle only, with a real
+    // diagonal (the contraction's lower mode), as LAPACK's hegst does; its mirror image is what the panel products
+    // below read - like the reference's hemm, which reads the stored triangle of A_kk only.
     if ((e = ops.gemm_nt(wk, wk, wk, R(1), wkk, (long long)nb, w.akk, w.ldk, R(0), w.tmp, w.ldk, 0)) != 0)
       return e;
-    if ((e = ops.gemm_nt(wk, wk, wk, R(1), w.tmp, w.ldk, wkk, (long long)nb, R(0), w.akk, w.ldk, 0)) != 0)
+    if ((e = ops.gemm_nt(wk, wk, wk, R(1), w.tmp, w.ldk, wkk, (long long)nb, R(0), w.akk, w.ldk, 1)) != 0)
       return e;
     if ((e = ops.lacpy('L', wk, wk, w.akk, w.ldk, akk_a, lda)) != 0)
       return e;
     if (m == 0)
       continue;
+    if ((e = ops.transpose(wk, wk, w.akk, w.ldk, w.tmp, w.ldk, 1, 'U')) != 0)
+      return e;
+    if ((e = ops.lacpy('L', wk, wk, w.akk, w.ldk, w.tmp, w.ldk)) != 0)
+      return e;
+    const T* herm = w.tmp;  // full Hermitian A_kk
     T* ark = A + r0 + (long long)k0 * lda;
     const T* lrk = L + r0 + (long long)k0 * ldl;
     T* p = w.pa;                                   // m x wk
@@ -106,7 +113,7 @@ int gen_to_std_lower(Ops& ops, int n, int nb, T* A, long long lda, const T* L, l
     // P = A_rk W^H - 1/2 L_rk A_kk
     if ((e = ops.gemm_nt(m, wk, wk, R(1), ark, lda, wkk, (long long)nb, R(0), p, w.ldp, 0)) != 0)
       return e;
-    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, w.akk, w.ldk, R(1), p, w.ldp, 0)) != 0)
+    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, herm, w.ldk, R(1), p, w.ldp, 0)) != 0)
       return e;
     // A_rr -= P L_rk^H + L_rk P^H on the lower triangle, as one contraction over K = 2 wk
     if ((e = ops.lacpy('G', m, wk, lrk, ldl, pa_l, w.ldp)) != 0)
@@ -118,7 +125,7 @@ int gen_to_std_lower(Ops& ops, int n, int nb, T* A, long long lda, const T* L, l
     if ((e = ops.gemm_nt(m, m, 2 * wk, R(-1), w.pa, w.ldp, w.pb, w.ldp, R(1), A + r0 + (long long)r0 * lda, lda, 1)) != 0)
       return e;
     // A_rk = P - 1/2 L_rk A_kk
-    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, w.akk, w.ldk, R(1), p, w.ldp, 0)) != 0)
+    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, herm, w.ldk, R(1), p, w.ldp, 0)) != 0)
       return e;
     if ((e = ops.lacpy('G', m, wk, p, w.ldp, ark, lda)) != 0)
       return e;

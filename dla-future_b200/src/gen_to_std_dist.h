@@ -141,12 +141,19 @@ int gen_to_std_dist_lower(Ops& ops, int n, int nb, int P, int Q, int pr, int pc,
         return e;
       if ((e = ops.gemm_nt(wk, wk, wk, R(1), wkk, (long long)nb, dk_a, ldk, R(0), w.tmp, ldk, 0)) != 0)
         return e;
-      if ((e = ops.gemm_nt(wk, wk, wk, R(1), w.tmp, ldk, wkk, (long long)nb, R(0), dk_a, ldk, 0)) != 0)
+      // the stored triangle only, with a real diagonal (see gen_to_std.h); its mirror image travels
+      if ((e = ops.gemm_nt(wk, wk, wk, R(1), w.tmp, ldk, wkk, (long long)nb, R(0), dk_a, ldk, 1)) != 0)
         return e;
       if ((e = ops.lacpy('L', wk, wk, dk_a, ldk, akk, lda)) != 0)
         return e;
-      if (more && (e = ops.lacpy('G', wk, wk, wkk, (long long)nb, dk_w, ldk)) != 0)
-        return e;
+      if (more) {
+        if ((e = ops.transpose(wk, wk, dk_a, ldk, w.tmp, ldk, 1, 'U')) != 0)
+          return e;
+        if ((e = ops.lacpy('U', wk, wk, w.tmp, ldk, dk_a, ldk)) != 0)  // the diagonal is real: both copies agree on it
+          return e;
+        if ((e = ops.lacpy('G', wk, wk, wkk, (long long)nb, dk_w, ldk)) != 0)
+          return e;
+      }
     }
     if (!more)
       break;

@@ -254,6 +254,8 @@ struct HostOps {
           T v = Tr<T>::scale(acc, alpha);
           if (beta != R(0))
             v = Tr<T>::add(v, Tr<T>::scale(C[i + j * ldc], beta));
+          if (Tr<T>::is_complex && lower && i == j)
+            v = Tr<T>::from_real(Tr<T>::real(v));  // the kernels' lower mode keeps the diagonal real (herk semantics)
           C[i + j * ldc] = v;
         }
       return 0;
