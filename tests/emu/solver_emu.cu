@@ -423,11 +423,9 @@ struct SimComm {
   }
 };
 
+// What the distributed templates need besides HostOps and the collectives: the strided tile inverse and zero-fill.
 template <class T>
-struct DistHostOps : HostOps<T> {
-  SimComm* row = nullptr;  // members ordered by grid column
-  SimComm* col = nullptr;  // members ordered by grid row
-  int me_row = 0, me_col = 0;  // my index inside them
+struct DistLocalOps : HostOps<T> {
   int tri_inverse_local(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w, int g0, int gstep, int row0,
                         int row_step, int col0, int col_step, int count) {
     TriInvParams p{n, nb, ldt, upper, unit, g0, gstep, row0, row_step, col0, col_step, count};
@@ -442,6 +440,15 @@ struct DistHostOps : HostOps<T> {
         a[i + j * lda] = Tr<T>::zero();
     return 0;
   }
+  int group_begin() { return 0; }  // the emulated collectives complete one by one; grouping changes nothing here
+  int group_end() { return 0; }
+};
+
+template <class T>
+struct DistHostOps : DistLocalOps<T> {
+  SimComm* row = nullptr;  // members ordered by grid column
+  SimComm* col = nullptr;  // members ordered by grid row
+  int me_row = 0, me_col = 0;  // my index inside them
   // every member must arrive with the same count: a mismatch is what NCCL would turn into a hang or corruption
   static int bcast(SimComm* c, int me, int root, T* p, size_t count) {
     c->ptr[me] = p;
@@ -476,8 +483,6 @@ struct DistHostOps : HostOps<T> {
         p[x] = nan_value<T>();
     return bad ? 9201 : 0;
   }
-  int group_begin() { return 0; }  // the shared-memory collectives complete one by one; grouping changes nothing here
-  int group_end() { return 0; }
   int bcast_row(int root, T* p, size_t count) { return bcast(row, me_row, root, p, count); }
   int bcast_col(int root, T* p, size_t count) { return bcast(col, me_col, root, p, count); }
   int reduce_row(int root, T* p, size_t count) { return reduce(row, me_row, root, p, count); }
@@ -650,6 +655,98 @@ int redistribute_emu(int P, int Q, char ordering, long long m, long long n, int 
   return 0;
 }
 
+// ---- one rank of a REAL process group: the collectives are callbacks into the test harness (torch.distributed / gloo)
+extern "C" {
+typedef int (*emu_bcast_fn)(int axis, int root, void* ptr, long long bytes);  // axis 0: my grid row, 1: my grid column
+typedef int (*emu_reduce_fn)(int axis, int root, void* ptr, long long count, int is_double);  // sum of real numbers
+typedef int (*emu_alltoallv_fn)(const void* sendbuf, const long long* send_off, const long long* send_cnt, void* recvbuf,
+                                const long long* recv_off, const long long* recv_cnt, int elem_bytes, int world);
+}
+
+template <class T>
+struct CallbackOps : DistLocalOps<T> {
+  emu_bcast_fn bc = nullptr;
+  emu_reduce_fn rd = nullptr;
+  static constexpr int kRealPerElem = Tr<T>::is_complex ? 2 : 1;
+  static constexpr int kIsDouble = sizeof(typename Tr<T>::Real) == 8;
+  int bcast_row(int root, T* p, size_t count) { return bc(0, root, p, (long long)(count * sizeof(T))); }
+  int bcast_col(int root, T* p, size_t count) { return bc(1, root, p, (long long)(count * sizeof(T))); }
+  int reduce_row(int root, T* p, size_t count) { return rd(0, root, p, (long long)count * kRealPerElem, kIsDouble); }
+  int reduce_col(int root, T* p, size_t count) { return rd(1, root, p, (long long)count * kRealPerElem, kIsDouble); }
+};
+
+template <class T>
+int solve_dist_rank(int P, int Q, int pr, int pc, int src_r, int src_c, char side, char uplo, char op, char diag, int m,
+                    int n, int mb, int nb, const void* alpha, const void* a, long long lda, void* b, long long ldb,
+                    emu_bcast_fn bc, emu_reduce_fn rd) {
+  TriDistDesc d{side, uplo, op, diag, m, n, mb, nb, P, Q, pr, pc, src_r, src_c};
+  const TriDistSizes sz = tri_dist_sizes(d);
+  Guarded<T> winv(sz.winv), pan(sz.pan), pan2(sz.pan2), xb(sz.xb), wkh(sz.wkh), bt(sz.bt);
+  TriDistWork<T> w{winv.data(), pan.data(), pan2.data(), xb.data(), wkh.data(), bt.data()};
+  CallbackOps<T> ops;
+  ops.bc = bc;
+  ops.rd = rd;
+  int e = triangular_solve_dist<T>(ops, d, *static_cast<const T*>(alpha), static_cast<const T*>(a), lda,
+                                   static_cast<T*>(b), ldb, w);
+  if (e == 0 && ops.hazards)
+    e = 9001;
+  if (e == 0 && !(winv.intact() && pan.intact() && pan2.intact() && xb.intact() && wkh.intact() && bt.intact()))
+    e = 9300;
+  return e;
+}
+
+template <class T>
+int gen_to_std_dist_rank(int P, int Q, int pr, int pc, int src_r, int src_c, char uplo, int n, int nb, void* a,
+                         long long lda, const void* f, long long ldf, emu_bcast_fn bc, emu_reduce_fn rd) {
+  G2sDistDesc d{uplo, n, nb, P, Q, pr, pc, src_r, src_c};
+  const G2sDistSizes sz = g2s_dist_sizes(d);
+  Guarded<T> winv(sz.winv), dk(sz.dk), tmp(sz.tmp), xr(sz.xr), yt(sz.ytiles), ac(sz.acopy), lc(sz.lcopy);
+  G2sDistWork<T> w{winv.data(), dk.data(), tmp.data(), xr.data(), yt.data(), ac.data(), lc.data()};
+  CallbackOps<T> ops;
+  ops.bc = bc;
+  ops.rd = rd;
+  int e = gen_to_std_dist<T>(ops, d, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  if (e == 0 && ops.hazards)
+    e = 9001;
+  if (e == 0 && !(winv.intact() && dk.intact() && tmp.intact() && xr.intact() && yt.intact() && ac.intact() && lc.intact()))
+    e = 9300;
+  return e;
+}
+
+template <class T>
+struct RedistCallbackOps {
+  const RedistLists* L;
+  emu_alltoallv_fn a2a;
+  int world;
+  int copy_rects(int which, const T* src, T* dst) {
+    const std::vector<CopyRect>& v = which == 0 ? L->pack : which == 1 ? L->self : L->unpack;
+    for (int b = 0; b < (int)v.size(); ++b)
+      for (int th = 0; th < kCopyRectThreads; ++th)
+        copy_rects_body<T>(v.data(), src, dst, b, th, kCopyRectThreads);
+    return 0;
+  }
+  int alltoallv(const T* sendbuf, T* recvbuf) {
+    return a2a(sendbuf, L->send_off.data(), L->send_cnt.data(), recvbuf, L->recv_off.data(), L->recv_cnt.data(),
+               (int)sizeof(T), world);
+  }
+};
+
+template <class T>
+int redistribute_rank(int P, int Q, int pr, int pc, char ordering, long long m, long long n, int mb_s, int nb_s, int sr_s,
+                      int sc_s, int mb_d, int nb_d, int sr_d, int sc_d, const void* src, long long ld_src, void* dst,
+                      long long ld_dst, emu_alltoallv_fn a2a) {
+  RedistDesc d{m, n, mb_s, nb_s, sr_s, sc_s, mb_d, nb_d, sr_d, sc_d, P, Q, pr, pc, ordering};
+  if (!redist_valid(d))
+    return 9401;
+  const RedistLists L = redist_build(d, ld_src, ld_dst);
+  Guarded<T> sb((size_t)L.send_total), rb((size_t)L.recv_total);
+  RedistCallbackOps<T> ops{&L, a2a, P * Q};
+  int e = redistribute<T>(ops, L, static_cast<const T*>(src), static_cast<T*>(dst), sb.data(), rb.data());
+  if (e == 0 && !(sb.intact() && rb.intact()))
+    e = 9300;
+  return e;
+}
+
 }  // namespace
 
 #define EMU_TYPED(X, T)                                                                                             \
@@ -667,6 +764,25 @@ int redistribute_emu(int P, int Q, char ordering, long long m, long long n, int 
   }                                                                                                                 \
   int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
     return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
+  }                                                                                                                 \
+  int emu_triangular_solver_dist_rank_##X(int P, int Q, int pr, int pc, int src_r, int src_c, char side, char uplo, \
+                                          char op, char diag, int m, int n, int mb, int nb, const void* alpha,      \
+                                          const void* a, long long lda, void* b, long long ldb, emu_bcast_fn bc,     \
+                                          emu_reduce_fn rd) {                                                        \
+    return solve_dist_rank<T>(P, Q, pr, pc, src_r, src_c, side, uplo, op, diag, m, n, mb, nb, alpha, a, lda, b, ldb, \
+                              bc, rd);                                                                              \
+  }                                                                                                                 \
+  int emu_gen_to_std_dist_rank_##X(int P, int Q, int pr, int pc, int src_r, int src_c, char uplo, int n, int nb,    \
+                                   void* a, long long lda, const void* f, long long ldf, emu_bcast_fn bc,           \
+                                   emu_reduce_fn rd) {                                                               \
+    return gen_to_std_dist_rank<T>(P, Q, pr, pc, src_r, src_c, uplo, n, nb, a, lda, f, ldf, bc, rd);                \
+  }                                                                                                                 \
+  int emu_redistribute_rank_##X(int P, int Q, int pr, int pc, char ordering, long long m, long long n, int mb_s,    \
+                                int nb_s, int sr_s, int sc_s, int mb_d, int nb_d, int sr_d, int sc_d,               \
+                                const void* src, long long ld_src, void* dst, long long ld_dst,                      \
+                                emu_alltoallv_fn a2a) {                                                              \
+    return redistribute_rank<T>(P, Q, pr, pc, ordering, m, n, mb_s, nb_s, sr_s, sc_s, mb_d, nb_d, sr_d, sc_d, src,  \
+                                ld_src, dst, ld_dst, a2a);                                                          \
   }                                                                                                                 \
   int emu_redistribute_##X(int P, int Q, char ordering, long long m, long long n, int mb_s, int nb_s, int sr_s,     \
                            int sc_s, int mb_d, int nb_d, int sr_d, int sc_d, void* const* src,                      \
