@@ -1,5 +1,5 @@
-"""N > 1 path of the distributed rows over a REAL process group on the CPU: two processes, torch.distributed with the
-gloo backend. Each process runs the product's algorithm template for ITS rank (tests/emu: the per-rank entry points of
+"""N > 1 path of the distributed rows over a REAL process group on the CPU: two processes (grids 1 x 2, 2 x 1) and four
+(2 x 2, where the row and the column communicators are both non-trivial), torch.distributed with the gloo backend. Each process runs the product's algorithm template for ITS rank (tests/emu: the per-rank entry points of
 solver_emu.cu), and every broadcast / reduction / all-to-all of the template is a callback into this file that performs
 it with torch.distributed on the row / column / world group - the same call sequence a rank issues to NCCL on the
 device (src/dist_device_ops.h). A rank that skipped or reordered a collective would hang or fail here as it would there.
@@ -166,8 +166,8 @@ def _worker(rank, world, grid, port, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("grid", [(1, 2), (2, 1)])
-def test_world_size_2_gloo(grid):
+@pytest.mark.parametrize("grid", [(1, 2), (2, 1), (2, 2)])
+def test_process_group_gloo(grid):
     import torch.multiprocessing as mp
     so = os.path.join(ROOT, "tests", "emu", "_build", "libsolver_emu.so")
     if not os.path.exists(so):
@@ -178,7 +178,8 @@ def test_world_size_2_gloo(grid):
     s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, grid, port, q)) for r in range(2)]
+    world = grid[0] * grid[1]
+    procs = [ctx.Process(target=_worker, args=(r, world, grid, port, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted(q.get(timeout=300) for _ in procs)
