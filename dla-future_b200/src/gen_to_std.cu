@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <new>
 
 #include "dist_device_ops.h"
@@ -13,11 +14,17 @@
 namespace dlafb {
 namespace {
 
-// Every operation goes to the caller's stream in program order.
+// Operations go to the current lane's stream in program order; without look-ahead there is one lane, the caller's
+// stream.
 template <class T>
 struct G2sDeviceOps {
   cudaStream_t s;
+  cudaStream_t lanes[2];
+  cudaEvent_t* events;
   using R = typename Tr<T>::Real;
+  void lane(int l) { s = lanes[l]; }
+  int signal(int ev) { return (int)cudaEventRecord(events[ev], s); }
+  int wait(int ev) { return (int)cudaStreamWaitEvent(s, events[ev], 0); }
   int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
               long long ldc, int lower) {
     return (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower);
@@ -34,6 +41,8 @@ struct G2sDeviceOps {
   }
 };
 
+constexpr int kG2sEvents = 5;
+
 struct G2sPlan {
   char type, uplo;
   int n, nb;
@@ -41,7 +50,29 @@ struct G2sPlan {
   void* base = nullptr;  // one allocation, parts at 256-byte aligned offsets
   size_t off_winv = 0, off_akk = 0, off_tmp = 0, off_pa = 0, off_pb = 0, off_acopy = 0, off_lcopy = 0;
   size_t bytes = 0;
-  ~G2sPlan() { cudaFree(base); }
+  // look-ahead (DLAFB_G2S_LOOKAHEAD=1, read when the plan is created): lane 0 = high-priority stream, lane 1 = bulk
+  int lookahead = 0;
+  cudaStream_t hp = nullptr, np = nullptr;
+  cudaEvent_t ev[kG2sEvents] = {};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  ~G2sPlan() {
+    if (hp)
+      cudaStreamSynchronize(hp);
+    if (np)
+      cudaStreamSynchronize(np);
+    for (cudaEvent_t e : ev)
+      if (e)
+        cudaEventDestroy(e);
+    if (ev_fork)
+      cudaEventDestroy(ev_fork);
+    if (ev_join)
+      cudaEventDestroy(ev_join);
+    if (hp)
+      cudaStreamDestroy(hp);
+    if (np)
+      cudaStreamDestroy(np);
+    cudaFree(base);
+  }
 };
 
 size_t align_up(size_t x) { return (x + 255) & ~size_t(255); }
@@ -60,8 +91,24 @@ int g2s_run_typed(G2sPlan& p, void* a, long long lda, const void* f, long long l
   w.acopy = reinterpret_cast<T*>(b + p.off_acopy);
   w.lcopy = reinterpret_cast<T*>(b + p.off_lcopy);
   w.ldc = g2s_ldp(p.n);
-  G2sDeviceOps<T> ops{s};
-  return gen_to_std<T>(ops, p.uplo, p.n, p.nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  if (!p.lookahead) {
+    G2sDeviceOps<T> ops{s, {s, s}, p.ev};
+    return gen_to_std<T>(ops, p.uplo, p.n, p.nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  }
+  w.lookahead = 1;
+  w.panel_stride = g2s_panel_elems(p.n, p.nb);
+  // fork from the caller's stream, join back into it
+  cudaError_t ce;
+  if ((ce = cudaEventRecord(p.ev_fork, s)) != cudaSuccess || (ce = cudaStreamWaitEvent(p.hp, p.ev_fork, 0)) != cudaSuccess)
+    return (int)ce;
+  G2sDeviceOps<T> ops{p.hp, {p.hp, p.np}, p.ev};
+  const int e = gen_to_std<T>(ops, p.uplo, p.n, p.nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  // join even after an error so that the caller's stream stays ordered after whatever was enqueued
+  cudaEventRecord(p.ev_join, p.np);
+  cudaStreamWaitEvent(p.hp, p.ev_join, 0);
+  cudaEventRecord(p.ev_join, p.hp);
+  cudaStreamWaitEvent(s, p.ev_join, 0);
+  return e;
 }
 
 struct G2sDistPlan {
@@ -105,6 +152,25 @@ int dlafb_gen_to_std_plan_create(dlafb_gen_to_std_plan_t* out, char type, char u
   p->n = (int)n;
   p->nb = (int)nb;
   p->elem = type == 's' ? 4 : type == 'z' ? 16 : 8;
+  const char* la = getenv("DLAFB_G2S_LOOKAHEAD");
+  p->lookahead = (la && la[0] == '1') ? 1 : 0;
+  if (n > 0 && p->lookahead) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    cudaError_t e = cudaStreamCreateWithPriority(&p->hp, cudaStreamNonBlocking, hi);
+    if (e == cudaSuccess)
+      e = cudaStreamCreateWithPriority(&p->np, cudaStreamNonBlocking, lo);
+    for (int i = 0; i < kG2sEvents && e == cudaSuccess; ++i)
+      e = cudaEventCreateWithFlags(&p->ev[i], cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming);
+    if (e == cudaSuccess)
+      e = cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming);
+    if (e != cudaSuccess) {
+      delete p;
+      return (int)e;
+    }
+  }
   if (n > 0) {
     size_t off = 0;
     auto part = [&](size_t elems) {
@@ -112,11 +178,12 @@ int dlafb_gen_to_std_plan_create(dlafb_gen_to_std_plan_t* out, char type, char u
       off = align_up(off + elems * p->elem);
       return at;
     };
+    const size_t copies = p->lookahead ? 2 : 1;  // the panels are double-buffered with look-ahead
     p->off_winv = part(g2s_winv_elems(p->n, p->nb));
     p->off_akk = part(g2s_tile_elems(p->nb));
     p->off_tmp = part(g2s_tile_elems(p->nb));
-    p->off_pa = part(g2s_panel_elems(p->n, p->nb));
-    p->off_pb = part(g2s_panel_elems(p->n, p->nb));
+    p->off_pa = part(copies * g2s_panel_elems(p->n, p->nb));
+    p->off_pb = part(copies * g2s_panel_elems(p->n, p->nb));
     p->off_acopy = part(g2s_copy_elems(p->n, uplo));
     p->off_lcopy = part(g2s_copy_elems(p->n, uplo));
     p->bytes = off;

@@ -59,7 +59,113 @@ struct GenToStdWork {
   T* acopy;  // uplo 'U' only: n x n (ldc) lower-triangular images of A and of the factor
   T* lcopy;
   long long ldc;
+  // look-ahead variant: two lanes (streams); pa and pb are double-buffered, the second copy panel_stride elements on
+  int lookahead = 0;
+  size_t panel_stride = 0;
 };
+
+// events of the look-ahead variant (Ops::signal / Ops::wait); same numbering as the solver's (triangular_solver.h)
+enum G2sEvent { kG2sPrologue = 0, kG2sPanel0 = 1, kG2sPanel1 = 2, kG2sBulk0 = 3, kG2sBulk1 = 4 };
+
+// Main loop of the lower algorithm with look-ahead: lane 0 carries the dependent chain of a step (diagonal tile,
+// panel P, the update of the NEXT block column only), lane 1 the update of everything beyond it ("bulk"), so that the
+// chain of step k+1 runs under the bulk update of step k instead of after it:
+//   lane 0:  chain(k) -> [bulk(k-1) done] next(k) -> finish column k -> chain(k+1) -> ...
+//   lane 1:  bulk(k-1) -> [panels of step k built] bulk(k) -> ...
+// bulk(k-1) also writes the block column that next(k) writes, hence the wait; the panels [P | L_rk], [L_rk | P] are
+// double-buffered because bulk(k) reads them while lane 0 builds those of step k+1; the last correction of column k
+// (P - 1/2 L_rk A_kk) goes straight into A so that the panel stays read-only once it is published.
+// Additional Ops: lane(l), signal(ev), wait(ev) as in triangular_solver.h.
+template <class T, class Ops>
+int g2s_main_loop_lookahead(Ops& ops, int n, int nb, T* A, long long lda, const T* L, long long ldl,
+                            const GenToStdWork<T>& w) {
+  using R = typename Tr<T>::Real;
+  int e;
+  const int nt = ceil_div(n, nb);
+  if ((e = ops.signal(kG2sPrologue)) != 0)
+    return e;
+  ops.lane(1);
+  if ((e = ops.wait(kG2sPrologue)) != 0)
+    return e;
+  ops.lane(0);
+  bool bulk_issued[2] = {false, false};
+  for (int k = 0; k < nt; ++k) {
+    const int k0 = k * nb;
+    const int wk = n - k0 < nb ? n - k0 : nb;
+    const int r0 = k0 + wk;
+    const int m = n - r0;
+    T* akk_a = A + k0 + (long long)k0 * lda;
+    const T* wkk = w.winv + (size_t)k * nb * nb;
+    T* pa = w.pa + (size_t)(k & 1) * w.panel_stride;
+    T* pb = w.pb + (size_t)(k & 1) * w.panel_stride;
+    // ---- lane 0: diagonal tile
+    if ((e = ops.transpose(wk, wk, akk_a, lda, w.akk, w.ldk, 1, 'U')) != 0)
+      return e;
+    if ((e = ops.lacpy('L', wk, wk, akk_a, lda, w.akk, w.ldk)) != 0)
+      return e;
+    if ((e = ops.gemm_nt(wk, wk, wk, R(1), wkk, (long long)nb, w.akk, w.ldk, R(0), w.tmp, w.ldk, 0)) != 0)
+      return e;
+    if ((e = ops.gemm_nt(wk, wk, wk, R(1), w.tmp, w.ldk, wkk, (long long)nb, R(0), w.akk, w.ldk, 1)) != 0)
+      return e;
+    if ((e = ops.lacpy('L', wk, wk, w.akk, w.ldk, akk_a, lda)) != 0)
+      return e;
+    if (m == 0)
+      break;
+    if ((e = ops.transpose(wk, wk, w.akk, w.ldk, w.tmp, w.ldk, 1, 'U')) != 0)
+      return e;
+    if ((e = ops.lacpy('L', wk, wk, w.akk, w.ldk, w.tmp, w.ldk)) != 0)
+      return e;
+    const T* herm = w.tmp;
+    T* ark = A + r0 + (long long)k0 * lda;
+    const T* lrk = L + r0 + (long long)k0 * ldl;
+    // ---- lane 0: panels of this step (their buffers were last read by bulk(k-2), which next(k-1) has waited for)
+    if ((e = ops.gemm_nt(m, wk, wk, R(1), ark, lda, wkk, (long long)nb, R(0), pa, w.ldp, 0)) != 0)
+      return e;
+    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, herm, w.ldk, R(1), pa, w.ldp, 0)) != 0)
+      return e;
+    if ((e = ops.lacpy('G', m, wk, lrk, ldl, pa + (long long)wk * w.ldp, w.ldp)) != 0)
+      return e;
+    if ((e = ops.lacpy('G', m, wk, lrk, ldl, pb, w.ldp)) != 0)
+      return e;
+    if ((e = ops.lacpy('G', m, wk, pa, w.ldp, pb + (long long)wk * w.ldp, w.ldp)) != 0)
+      return e;
+    if ((e = ops.signal(kG2sPanel0 + (k & 1))) != 0)
+      return e;
+    // ---- lane 0: update of the next block column (rows r0.., columns r0 .. r0 + wn); bulk(k-1) wrote it too
+    const int wn = m < nb ? m : nb;
+    if (k >= 1 && bulk_issued[(k - 1) & 1] && (e = ops.wait(kG2sBulk0 + ((k - 1) & 1))) != 0)
+      return e;
+    T* arr = A + r0 + (long long)r0 * lda;
+    if ((e = ops.gemm_nt(wn, wn, 2 * wk, R(-1), pa, w.ldp, pb, w.ldp, R(1), arr, lda, 1)) != 0)  // its diagonal tile
+      return e;
+    if (m > wn && (e = ops.gemm_nt(m - wn, wn, 2 * wk, R(-1), pa + wn, w.ldp, pb, w.ldp, R(1), arr + wn, lda, 0)) != 0)
+      return e;
+    // ---- lane 0: column k is finished directly in A (the published panel stays untouched)
+    if ((e = ops.lacpy('G', m, wk, pa, w.ldp, ark, lda)) != 0)
+      return e;
+    if ((e = ops.gemm_nt(m, wk, wk, R(-0.5), lrk, ldl, herm, w.ldk, R(1), ark, lda, 0)) != 0)
+      return e;
+    // ---- lane 1: everything beyond the next block column
+    const int mb = m - wn;
+    bulk_issued[k & 1] = mb > 0;
+    if (mb > 0) {
+      ops.lane(1);
+      if ((e = ops.wait(kG2sPanel0 + (k & 1))) != 0)
+        return e;
+      if ((e = ops.gemm_nt(mb, mb, 2 * wk, R(-1), pa + wn, w.ldp, pb + wn, w.ldp, R(1),
+                           arr + wn + (long long)wn * lda, lda, 1)) != 0)
+        return e;
+      if ((e = ops.signal(kG2sBulk0 + (k & 1))) != 0)
+        return e;
+      ops.lane(0);
+    }
+  }
+  // join: everything lane 1 did is ordered before what follows on lane 0
+  for (int q = 0; q < 2; ++q)
+    if (bulk_issued[q] && (e = ops.wait(kG2sBulk0 + q)) != 0)
+      return e;
+  return 0;
+}
 
 // Ops interface (all return 0 on success; semantics of the device launchers in tile_ops.cuh):
 //   gemm_nt(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower)   C <- beta C + alpha A B^H; lower: rows >= cols only
@@ -77,7 +183,9 @@ int gen_to_std_lower(Ops& ops, int n, int nb, T* A, long long lda, const T* L, l
   if ((e = ops.tri_inverse(0, 0, n, nb, L, ldl, w.winv)) != 0)
     return e;
 
-  for (int k = 0; k < nt; ++k) {
+  if (w.lookahead && (e = g2s_main_loop_lookahead<T>(ops, n, nb, A, lda, L, ldl, w)) != 0)
+    return e;
+  for (int k = 0; k < nt && !w.lookahead; ++k) {
     const int k0 = k * nb;
     const int wk = n - k0 < nb ? n - k0 : nb;
     const int r0 = k0 + wk;

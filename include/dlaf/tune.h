@@ -18,6 +18,9 @@ struct TuneParameters {
   int bulk_update_shape = env_int("DLAFB_BULK_SHAPE", 3);
   /// DLAFB_TRSOLVE_LOOKAHEAD: two-stream look-ahead variant of the one-GPU triangular solver. Read at plan creation.
   int triangular_solver_lookahead = env_int("DLAFB_TRSOLVE_LOOKAHEAD", 0);
+  /// DLAFB_G2S_LOOKAHEAD: two-stream look-ahead variant of the one-GPU generalized-to-standard reduction. Read at plan
+  /// creation.
+  int gen_to_std_lookahead = env_int("DLAFB_G2S_LOOKAHEAD", 0);
   /// DLAFB_SGEMM_WIDE [process]: float contractions on the 128x128 kernel (off until timed on the device).
   int sgemm_wide = env_int("DLAFB_SGEMM_WIDE", 0);
   /// DLAFB_POTRF_REDISTRIBUTE: dlaf_p?potrf redistributes matrices with block sizes below 256 to <= 512, factorizes and
@@ -29,6 +32,7 @@ struct TuneParameters {
     set("DLAFB_P2P", peer_memory_exchange);
     set("DLAFB_BULK_SHAPE", bulk_update_shape);
     set("DLAFB_TRSOLVE_LOOKAHEAD", triangular_solver_lookahead);
+    set("DLAFB_G2S_LOOKAHEAD", gen_to_std_lookahead);
     set("DLAFB_SGEMM_WIDE", sgemm_wide);
     set("DLAFB_POTRF_REDISTRIBUTE", potrf_redistribute);
   }

@@ -386,14 +386,30 @@ int inverse(int upper, int unit, int n, int nb, const void* t, long long ldt, vo
 }
 
 // Generalized-to-standard reduction: the product's algorithm template over the host executor, NaN-filled workspaces.
+// lookahead = 0: one lane, immediate. lookahead = 1: the two-lane variant, replayed with lane `prefer` running
+// whenever it can; *races = number of unordered operation pairs with overlapping operands.
 template <class T>
-int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {
-  Guarded<T> winv(g2s_winv_elems(n, nb)), akk(g2s_tile_elems(nb)), tmp(g2s_tile_elems(nb)), pa(g2s_panel_elems(n, nb)),
-      pb(g2s_panel_elems(n, nb)), ac(g2s_copy_elems(n, uplo)), lc(g2s_copy_elems(n, uplo));
+int gen_to_std_emu(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf, int lookahead = 0,
+                   int prefer = 0, int* races = nullptr) {
+  const size_t copies = lookahead ? 2 : 1;
+  Guarded<T> winv(g2s_winv_elems(n, nb)), akk(g2s_tile_elems(nb)), tmp(g2s_tile_elems(nb)),
+      pa(copies * g2s_panel_elems(n, nb)), pb(copies * g2s_panel_elems(n, nb)), ac(g2s_copy_elems(n, uplo)),
+      lc(g2s_copy_elems(n, uplo));
   GenToStdWork<T> w{winv.data(), akk.data(), tmp.data(), g2s_even(nb), pa.data(), pb.data(), g2s_ldp(n),
                     ac.data(), lc.data(), g2s_ldp(n)};
   HostOps<T> ops;
-  const int e = gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  if (lookahead) {
+    w.lookahead = 1;
+    w.panel_stride = g2s_panel_elems(n, nb);
+    ops.deferred = true;
+  }
+  int e = gen_to_std<T>(ops, uplo, n, nb, static_cast<T*>(a), lda, static_cast<const T*>(f), ldf, w);
+  if (lookahead) {
+    if (e == 0)
+      e = ops.drain(prefer);
+    if (races)
+      *races = ops.races();
+  }
   if (e == 0 && !(winv.intact() && akk.intact() && tmp.intact() && pa.intact() && pb.intact() && ac.intact() && lc.intact()))
     return 9300;
   return e;
@@ -764,6 +780,10 @@ int redistribute_rank(int P, int Q, int pr, int pc, char ordering, long long m, 
   }                                                                                                                 \
   int emu_gen_to_std_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf) {          \
     return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf);                                                          \
+  }                                                                                                                 \
+  int emu_gen_to_std_la_##X(char uplo, int n, int nb, void* a, long long lda, const void* f, long long ldf,        \
+                            int prefer, int* races) {                                                               \
+    return gen_to_std_emu<T>(uplo, n, nb, a, lda, f, ldf, 1, prefer, races);                                        \
   }                                                                                                                 \
   int emu_triangular_solver_dist_rank_##X(int P, int Q, int pr, int pc, int src_r, int src_c, char side, char uplo, \
                                           char op, char diag, int m, int n, int mb, int nb, const void* alpha,      \
