@@ -2,7 +2,8 @@
 miniapp_gen_to_std metric: flops = total_ops<T>(n^3 / 2, n^3 / 2) (miniapp/miniapp_gen_to_std.cpp), i.e. n^3 real /
 4 n^3 complex; device-resident operands, CUDA events around the reduction.
 
-  python profiles/tools/bench_gen_to_std.py [type uplo n nb] ...
+  python profiles/tools/bench_gen_to_std.py [--both] [type uplo n nb] ...
+  --both: every case with DLAFB_G2S_LOOKAHEAD=0 and =1 (the variable is read when the plan is created)
   default: d L 16384 512, d U 16384 512, z L 8192 512, s L 16384 512, d L 32768 512
 
 Check (torch.matmul / triangular solves as the checker only): with C the result, max|L C L^H - A| / (max|A| n eps)
@@ -67,12 +68,19 @@ def main():
     L = pkg.lib()
     torch.cuda.set_device(0)
     args = sys.argv[1:]
+    both = "--both" in args
+    args = [a for a in args if a != "--both"]
     cases = [(args[i], args[i + 1], int(args[i + 2]), int(args[i + 3])) for i in range(0, len(args), 4)] or \
         [("d", "L", 16384, 512), ("d", "U", 16384, 512), ("z", "L", 8192, 512), ("s", "L", 16384, 512),
          ("d", "L", 32768, 512)]
     for c in cases:
-        print(json.dumps(run(pkg, L, *c)), flush=True)
-        torch.cuda.empty_cache()
+        for la in (("0", "1") if both else (os.environ.get("DLAFB_G2S_LOOKAHEAD"),)):
+            if la is not None:
+                os.environ["DLAFB_G2S_LOOKAHEAD"] = la
+            r = run(pkg, L, *c)
+            r["lookahead"] = la if la is not None else "default"
+            print(json.dumps(r), flush=True)
+            torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":

@@ -37,7 +37,7 @@ one)
   for t in gen_to_std triangular_dist submatrix redistribute max_norm sgemm_wide; do
     step "tests_$t" 900 $PY -m pytest "tests/test_zz_${t}_gpu.py" -q -m gpu
   done
-  step bench_gen_to_std 600 $PY profiles/tools/bench_gen_to_std.py
+  step bench_gen_to_std 900 $PY profiles/tools/bench_gen_to_std.py --both
   step bench_dist_rows_1x1 600 $PY profiles/tools/bench_dist_rows.py --n 32768 --nb 512
   step bench_redistribute 300 $PY profiles/tools/bench_redistribute.py --n 32768 --nb-src 64 --nb-dst 512
   step bench_types_default 600 $PY profiles/tools/bench_types.py
