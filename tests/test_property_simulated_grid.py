@@ -97,3 +97,62 @@ def test_distributed_reduction_matches_the_dense_formula(g2s_emu_fixture, grid, 
     want = sla.solve(lfac, sla.solve(lfac, a_full).conj().T).conj().T     # L^-1 A L^-H
     assert np.all(np.isnan(got[~keep]))
     assert np.abs(got[keep] - want[keep]).max() <= 1e-11 * n * max(1.0, np.abs(want).max())
+
+
+# ---- the one-GPU templates (single lane and the two-lane look-ahead variants with race detection) --------------------
+from test_gen_to_std_emu import emu as g2s_local_emu_fixture  # noqa: E402,F401
+from test_gen_to_std_emu import run as g2s_local_run  # noqa: E402
+from test_triangular_emu import emu as tri_local_emu_fixture  # noqa: E402,F401
+from test_triangular_emu import run as tri_local_run  # noqa: E402
+
+
+@settings(**COMMON)
+@given(side=st.sampled_from("LR"), uplo=st.sampled_from("LU"), op=st.sampled_from("NTC"), diag=st.sampled_from("NU"),
+       m=st.integers(1, 40), n=st.integers(1, 40), nb=st.integers(1, 11), x=st.sampled_from("sdcz"),
+       lookahead=st.sampled_from([None, 0, 1]), seed=st.integers(0, 10 ** 6))
+def test_local_solve_satisfies_the_equation(tri_local_emu_fixture, side, uplo, op, diag, m, n, nb, x, lookahead, seed):  # noqa: F811
+    dt = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}[x]
+    rng = np.random.default_rng(seed)
+    na = m if side == "L" else n
+    cplx = np.dtype(dt).kind == "c"
+    a = rng.standard_normal((na, na)) + (1j * rng.standard_normal((na, na)) if cplx else 0)
+    a = (a / max(1.0, np.sqrt(na)) + 2 * np.eye(na) * np.sign(rng.standard_normal(na))).astype(dt)
+    b = (rng.standard_normal((m, n)) + (1j * rng.standard_normal((m, n)) if cplx else 0)).astype(dt)
+    tri = np.tril(a) if uplo == "L" else np.triu(a)
+    if diag == "U":
+        np.fill_diagonal(tri, 1)
+    unref = np.triu(np.ones(a.shape, bool), 1) if uplo == "L" else np.tril(np.ones(a.shape, bool), -1)
+    if diag == "U":
+        unref |= np.eye(na, dtype=bool)
+    a[unref] = np.nan
+    alpha = orc.triangular_test_alpha(dt)
+    got = tri_local_run(tri_local_emu_fixture, x, side, uplo, op, diag, alpha, a, b, nb, pad_a=seed % 2, pad_b=seed % 3,
+                        lookahead=lookahead)
+    wide = np.complex128 if cplx else np.float64
+    opa = (tri if op == "N" else tri.T if op == "T" else tri.conj().T).astype(wide)
+    lhs = opa @ got.astype(wide) if side == "L" else got.astype(wide) @ opa
+    scale = np.abs(opa).max() * max(1.0, np.abs(got).max()) * max(m, n)
+    assert np.abs(lhs - wide(alpha) * b.astype(wide)).max() <= 20 * np.finfo(dt).eps * scale * np.linalg.cond(opa)
+
+
+@settings(**COMMON)
+@given(uplo=st.sampled_from("LU"), n=st.integers(1, 48), nb=st.integers(1, 11), x=st.sampled_from("dz"),
+       lookahead=st.sampled_from([None, 0, 1]), seed=st.integers(0, 10 ** 6))
+def test_local_reduction_matches_the_dense_formula(g2s_local_emu_fixture, uplo, n, nb, x, lookahead, seed):  # noqa: F811
+    dt = {"d": np.float64, "z": np.complex128}[x]
+    rng = np.random.default_rng(seed)
+    cplx = x == "z"
+    g = rng.standard_normal((n, n)) + (1j * rng.standard_normal((n, n)) if cplx else 0)
+    a_full = (g + g.conj().T).astype(dt)
+    a_full[np.diag_indices(n)] = a_full.diagonal().real
+    h = rng.standard_normal((n, n)) + (1j * rng.standard_normal((n, n)) if cplx else 0)
+    lfac = np.linalg.cholesky((h @ h.conj().T + n * np.eye(n)).astype(dt))
+    keep = (np.tril if uplo == "L" else np.triu)(np.ones((n, n))) > 0
+    fac = lfac if uplo == "L" else lfac.conj().T
+    got = g2s_local_run(g2s_local_emu_fixture, x, uplo, np.where(keep, a_full, np.nan).astype(dt),
+                        np.where(keep, fac, np.nan).astype(dt), nb, pad_a=seed % 2, lookahead=lookahead)
+    want = sla.solve(lfac, sla.solve(lfac, a_full).conj().T).conj().T
+    assert np.all(np.isnan(got[~keep]))
+    assert np.abs(got[keep] - want[keep]).max() <= 1e-11 * n * max(1.0, np.abs(want).max())
+    if cplx:
+        assert np.all(got[np.diag_indices(n)].imag == 0)   # the reduced matrix keeps a real diagonal, as hegst does
