@@ -65,6 +65,13 @@ eight)
   step bench_dist_rows_2x4 1200 torchrun_n 8 29941 profiles/tools/bench_dist_rows.py --n 65536 --nb 512
   step bench_redistribute_2x4 300 torchrun_n 8 29942 profiles/tools/bench_redistribute.py --n 65536
   step bench8 900 torchrun_n 8 29943 bench.py --gpus 8 --steps 3 --warmup 3
+  # the other BASELINE.json configurations at 8 GPUs: complex double, float (default and wide kernel), weak scaling
+  step config3_z 900 torchrun_n 8 29944 profiles/tools/bench_dist_types.py --type z --n 40960 --nb 512
+  step config4_s 900 torchrun_n 8 29945 profiles/tools/bench_dist_types.py --type s --n 65536 --nb 512
+  step config4_s_wide 900 env DLAFB_SGEMM_WIDE=1 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node 8 \
+      --master-addr 127.0.0.1 --master-port 29946 profiles/tools/bench_dist_types.py --type s --n 65536 --nb 512
+  step config4_weak8 1200 torchrun_n 8 29947 profiles/tools/bench_dist_types.py --type d --n 92160 --nb 1024
+  step config4_weak8_ragged 1200 torchrun_n 8 29948 profiles/tools/bench_dist_types.py --type d --n 92682 --nb 1024 --no-check
   ;;
 *)
   echo "usage: $0 one|two|eight" >&2
