@@ -9,6 +9,7 @@
 #include "dist_device_ops.h"
 #include "dlafb_gen_to_std.h"
 #include "gen_to_std_dist.h"
+#include "op_trace.h"
 #include "tile_ops.cuh"
 
 namespace dlafb {
@@ -27,17 +28,24 @@ struct G2sDeviceOps {
   int wait(int ev) { return (int)cudaStreamWaitEvent(s, events[ev], 0); }
   int gemm_nt(int M, int N, int K, R alpha, const T* A, long long lda, const T* B, long long ldb, R beta, T* C,
               long long ldc, int lower) {
-    return (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower);
+    DLAFB_TRACE_OP("gemm_nt M=%d N=%d K=%d alpha=%g beta=%g lower=%d A=%p lda=%lld B=%p ldb=%lld C=%p ldc=%lld", M, N, K,
+                   (double)alpha, (double)beta, lower, (const void*)A, lda, (const void*)B, ldb, (void*)C, ldc);
+    return op_trace_finish(s, (int)dlafb::gemm_nt<T>(s, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, lower), "gemm_nt");
   }
   int transpose(int m, int n, const T* in, long long ldin, T* out, long long ldout, int conj, char tri) {
-    return (int)dlafb::transpose<T>(s, m, n, in, ldin, out, ldout, conj, tri);
+    DLAFB_TRACE_OP("transpose m=%d n=%d conj=%d tri=%c in=%p ldin=%lld out=%p ldout=%lld", m, n, conj, tri, (const void*)in,
+                   ldin, (void*)out, ldout);
+    return op_trace_finish(s, (int)dlafb::transpose<T>(s, m, n, in, ldin, out, ldout, conj, tri), "transpose");
   }
   int lacpy(char uplo, int m, int n, const T* a, long long lda, T* b, long long ldb) {
-    return (int)dlafb::lacpy<T>(s, uplo, m, n, a, lda, b, ldb);
+    DLAFB_TRACE_OP("lacpy %c m=%d n=%d a=%p lda=%lld b=%p ldb=%lld", uplo, m, n, (const void*)a, lda, (void*)b, ldb);
+    return op_trace_finish(s, (int)dlafb::lacpy<T>(s, uplo, m, n, a, lda, b, ldb), "lacpy");
   }
   int tri_inverse(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w) {
     TriInvParams p{n, nb, ldt, upper, unit};
-    return (int)launch_tri_inverse<T>(s, p, t, w);
+    DLAFB_TRACE_OP("tri_inverse upper=%d unit=%d n=%d nb=%d t=%p ldt=%lld w=%p", upper, unit, n, nb, (const void*)t, ldt,
+                   (void*)w);
+    return op_trace_finish(s, (int)launch_tri_inverse<T>(s, p, t, w), "tri_inverse");
   }
 };
 
