@@ -22,6 +22,7 @@
 #include <thread>
 
 #include "gen_to_std.h"
+#include "op_trace.h"
 #include "redistribute.h"
 #include "gen_to_std_dist.h"
 #include "triangular_solver.h"
@@ -236,6 +237,9 @@ struct HostOps {
               long long ldc, int lower = 0) {
     if (M <= 0 || N <= 0)
       return 0;
+    // same line format as the device executors (src/op_trace.h) so that the two logs can be compared
+    DLAFB_TRACE_OP("gemm_nt M=%d N=%d K=%d alpha=%g beta=%g lower=%d A=%p lda=%lld B=%p ldb=%lld C=%p ldc=%lld", M, N, K,
+                   (double)alpha, (double)beta, lower, (const void*)A, lda, (const void*)B, ldb, (void*)C, ldc);
     Op op;
     op.reads = {rect(A, lda, M, K), rect(B, ldb, N, K)};
     if (beta != R(0))
@@ -266,6 +270,8 @@ struct HostOps {
   int transpose(int m, int n, const T* in, long long ldin, T* out, long long ldout, int conj, char tri) {
     if (m <= 0 || n <= 0)
       return 0;
+    DLAFB_TRACE_OP("transpose m=%d n=%d conj=%d tri=%c in=%p ldin=%lld out=%p ldout=%lld", m, n, conj, tri, (const void*)in,
+                   ldin, (void*)out, ldout);
     Op op;
     op.reads = {rect(in, ldin, m, n)};
     op.writes = {rect(out, ldout, n, m)};
@@ -303,6 +309,7 @@ struct HostOps {
   int lacpy(char uplo, int m, int n, const T* a, long long lda, T* b, long long ldb) {
     if (m <= 0 || n <= 0)
       return 0;
+    DLAFB_TRACE_OP("lacpy %c m=%d n=%d a=%p lda=%lld b=%p ldb=%lld", uplo, m, n, (const void*)a, lda, (void*)b, ldb);
     Op op;
     op.reads = {rect(a, lda, m, n)};
     op.writes = {rect(b, ldb, m, n)};
@@ -322,6 +329,8 @@ struct HostOps {
     return issue(std::move(op));
   }
   int tri_inverse(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w) {
+    DLAFB_TRACE_OP("tri_inverse upper=%d unit=%d n=%d nb=%d t=%p ldt=%lld w=%p", upper, unit, n, nb, (const void*)t, ldt,
+                   (void*)w);
     Op op;
     op.reads = {rect(t, ldt, n, n)};
     op.writes = {rect(w, 1, tri_inverse_blocks(n, nb) * nb * nb, 1)};
@@ -338,6 +347,7 @@ struct HostOps {
   int scale(int m, int n, T* b, long long ldb, T alpha, int conj) {
     if (m <= 0 || n <= 0)
       return 0;
+    DLAFB_TRACE_OP("scale m=%d n=%d conj=%d b=%p ldb=%lld", m, n, conj, (void*)b, ldb);
     Op op;
     op.reads = {rect(b, ldb, m, n)};
     op.writes = {rect(b, ldb, m, n)};
@@ -445,12 +455,15 @@ struct DistLocalOps : HostOps<T> {
   int tri_inverse_local(int upper, int unit, int n, int nb, const T* t, long long ldt, T* w, int g0, int gstep, int row0,
                         int row_step, int col0, int col_step, int count) {
     TriInvParams p{n, nb, ldt, upper, unit, g0, gstep, row0, row_step, col0, col_step, count};
+    DLAFB_TRACE_OP("tri_inverse upper=%d unit=%d n=%d nb=%d t=%p ldt=%lld w=%p g0=%d gstep=%d count=%d", upper, unit, n, nb,
+                   (const void*)t, ldt, (void*)w, g0, gstep, count);
     for (int b = 0; b < count; ++b)
       for (int th = 0; th < kTriInvThreads; ++th)
         tri_inverse_body<T>(p, t, w, b, th, kTriInvThreads);
     return 0;
   }
   int zero(int m, int n, T* a, long long lda) {
+    DLAFB_TRACE_OP("zero m=%d n=%d a=%p lda=%lld", m, n, (void*)a, lda);
     for (int j = 0; j < n; ++j)
       for (int i = 0; i < m; ++i)
         a[i + j * lda] = Tr<T>::zero();
@@ -499,10 +512,22 @@ struct DistHostOps : DistLocalOps<T> {
         p[x] = nan_value<T>();
     return bad ? 9201 : 0;
   }
-  int bcast_row(int root, T* p, size_t count) { return bcast(row, me_row, root, p, count); }
-  int bcast_col(int root, T* p, size_t count) { return bcast(col, me_col, root, p, count); }
-  int reduce_row(int root, T* p, size_t count) { return reduce(row, me_row, root, p, count); }
-  int reduce_col(int root, T* p, size_t count) { return reduce(col, me_col, root, p, count); }
+  int bcast_row(int root, T* p, size_t count) {
+    DLAFB_TRACE_OP("bcast_row root=%d count=%zu p=%p", root, count, (void*)p);
+    return bcast(row, me_row, root, p, count);
+  }
+  int bcast_col(int root, T* p, size_t count) {
+    DLAFB_TRACE_OP("bcast_col root=%d count=%zu p=%p", root, count, (void*)p);
+    return bcast(col, me_col, root, p, count);
+  }
+  int reduce_row(int root, T* p, size_t count) {
+    DLAFB_TRACE_OP("reduce_row root=%d count=%zu p=%p", root, count, (void*)p);
+    return reduce(row, me_row, root, p, count);
+  }
+  int reduce_col(int root, T* p, size_t count) {
+    DLAFB_TRACE_OP("reduce_col root=%d count=%zu p=%p", root, count, (void*)p);
+    return reduce(col, me_col, root, p, count);
+  }
 };
 
 // All the ranks of a P x Q grid in one process; a[r], b[r] = local blocks of rank r = pr * Q + pc.
