@@ -1,5 +1,5 @@
 // comm::Communicator: thin value wrapper of an MPI_Comm (reference: include/dlaf/communication/communicator.h,
-// src/communication/communicator_impl.cpp). <mpi.h> is the real one with DLAFB_WITH_MPI, else the single-node shim.
+// src/communication/communicator_impl.cpp). <mpi.h> is the single-node shim include/dlafb_mpi_shim/mpi.h.
 #pragma once
 #include <mpi.h>
 

@@ -1,6 +1,6 @@
 /* Process-grid registry of the C API (reference: include/dlaf_c/grid.h:31-74, src/c_api/grid.cpp:26-92).
- * MPI_Comm comes from <mpi.h>: a real MPI when the build defines DLAFB_WITH_MPI, otherwise the single-node shim
- * in include/dlafb_mpi_shim/mpi.h (ranks = processes, one per GPU, bootstrapped with an NCCL unique id). */
+ * MPI_Comm comes from <mpi.h> = the single-node shim in include/dlafb_mpi_shim/mpi.h (ranks = processes, one per GPU,
+ * bootstrapped with an NCCL unique id; see that header for applications that use a real MPI). */
 #pragma once
 #include <mpi.h>
 

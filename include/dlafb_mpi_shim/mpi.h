@@ -2,7 +2,9 @@
  * It keeps the MPI_Comm-typed signatures of the reference's C and C++ APIs compiling and gives them meaning for
  * the one-process-per-GPU launch this build targets: a communicator is {rank, size, NCCL unique id}; the
  * launcher (torchrun + torch.distributed, or any other) distributes the unique id and calls dlafb_mpi_init.
- * With a real MPI define DLAFB_WITH_MPI and put the real <mpi.h> first on the include path instead. */
+ * An application that uses a real MPI bootstraps this handle with its own rank / size and an id it broadcasts with
+ * MPI_Bcast, from a translation unit that includes this header and not the real <mpi.h> (both define MPI_Comm);
+ * passing real MPI communicators into the library is not supported in this build. */
 #ifndef DLAFB_MPI_SHIM_H
 #define DLAFB_MPI_SHIM_H
 
