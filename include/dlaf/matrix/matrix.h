@@ -7,6 +7,7 @@
 
 #include <functional>
 #include <memory>
+#include <vector>
 #include <utility>
 
 #include "dlaf/communication/communicator_grid.h"
@@ -68,7 +69,7 @@ public:
   ~Matrix() {
     if (stream_) {
       cudaStreamSynchronize(stream_);
-      keep_alive_.reset();
+      keep_alive_.clear();
       cudaStreamDestroy(stream_);
     }
     if (owned_) {
@@ -112,17 +113,22 @@ public:
   /// Blocks until every operation enqueued on the local tiles has completed (matrix.h:322-338).
   void waitLocalTiles() noexcept {
     cudaStreamSynchronize(stream_);
-    if (on_wait_) {
-      auto f = std::move(on_wait_);
-      on_wait_ = nullptr;
-      f();
-    }
+    // completion hooks of the algorithms enqueued since the last wait (e.g. the factorization's info check), in
+    // order; then the resources they parked are released - nothing on the stream can still be using them
+    auto hooks = std::move(on_wait_);
+    on_wait_.clear();
+    for (auto& f : hooks)
+      f();  // the hooks may use the parked resources (the factorization's plan): release those afterwards
+    keep_alive_.clear();
   }
 
-  /// Internal: algorithms park resources that must outlive the enqueued work, and a completion hook.
+  /// Internal: algorithms park resources that must outlive the enqueued work, and a completion hook. Several
+  /// algorithms may be enqueued on the same matrix before it is waited for: everything is kept until then.
   void keep_alive(std::shared_ptr<void> p, std::function<void()> on_wait = nullptr) {
-    keep_alive_ = std::move(p);
-    on_wait_ = std::move(on_wait);
+    if (p)
+      keep_alive_.push_back(std::move(p));
+    if (on_wait)
+      on_wait_.push_back(std::move(on_wait));
   }
 
 private:
@@ -153,8 +159,8 @@ private:
   T* ptr_ = nullptr;
   void* owned_ = nullptr;
   cudaStream_t stream_ = nullptr;
-  std::shared_ptr<void> keep_alive_;
-  std::function<void()> on_wait_;
+  std::vector<std::shared_ptr<void>> keep_alive_;
+  std::vector<std::function<void()>> on_wait_;
 };
 
 /// Copies the local block between two matrices with the same distribution, on the destination's stream
