@@ -19,3 +19,21 @@ def test_front_ends_instantiate_for_all_types():
            os.path.join(ROOT, "tests", "cxx", "api_compile.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_c_headers_are_plain_c_and_every_symbol_links(pkg, tmp_path):
+    """The drop-in boundary is a C ABI: every public C header must compile as C99 (no C++-isms) and the functions it
+    declares must link from a C program against the shared library (C linkage, no mangling). Not run."""
+    if shutil.which("gcc") is None:
+        pytest.skip("needs gcc")
+    src = os.path.join(ROOT, "tests", "cxx", "c_headers.c")
+    inc = ["-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "include", "dlafb_mpi_shim")]
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only"] + inc + [src],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    if not os.path.exists(pkg.LIB_PATH):
+        pytest.skip("library not built")
+    libdir = os.path.dirname(pkg.LIB_PATH)
+    r = subprocess.run(["gcc", "-std=c99"] + inc + [src, "-o", str(tmp_path / "c_link"), "-L" + libdir, "-ldlaf_b200",
+                        "-Wl,-rpath," + libdir, "-Wl,--allow-shlib-undefined"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
