@@ -1,6 +1,12 @@
 // TEST INFRASTRUCTURE: instantiates every public C++ front end of include/dlaf/ for the four element types, so that
 // the CPU test-suite (tests/test_cxx_headers.py) catches a header that no longer compiles. Never run.
 #include "dlaf/auxiliary/norm.h"
+#include "dlaf/common/range2d.h"
+#include "dlaf/factorization.h"
+#include "dlaf/matrix/index.h"
+#include "dlaf/matrix/matrix_mirror.h"
+#include "dlaf/solver.h"
+#include "dlaf/util_matrix.h"
 #include "dlaf/common/round_robin.h"
 #include "dlaf/common/timer.h"
 #include "dlaf/tune.h"
@@ -29,6 +35,22 @@ void instantiate(dlaf::comm::CommunicatorGrid& grid) {
   matrix::copy(c, d, grid);
   d.waitLocalTiles();
   (void)auxiliary::max_norm<Backend::GPU, Device::GPU, T>(grid, comm::Index2D(0, 0), blas::Uplo::Lower, d);
+  matrix::util::set_random_hermitian_positive_definite(a);
+  matrix::util::set_random_hermitian(b);
+  matrix::util::set0(c);
+  Matrix<T, Device::CPU> h(LocalElementSize(8, 8), TileElementSize(4, 4));
+  matrix::util::set_random_hermitian_positive_definite(h);
+  {
+    matrix::MatrixMirror<T, Device::GPU, Device::CPU> mirror(h);
+    cholesky_factorization<Backend::GPU, Device::GPU, T>(blas::Uplo::Lower, mirror.get());
+  }
+  (void)(matrix::square_size(a) && matrix::square_blocksize(a) && matrix::local_matrix(a) && matrix::equal_process_grid(c, grid));
+  SizeType count = 0;
+  for (auto ij : common::iterate_range2d(a.distribution().local_nr_tiles()))
+    count += a.read(ij).size().rows();
+  for (auto ij : common::iterate_range2d(LocalTileIndex(1, 0), LocalTileIndex(2, 2)))
+    count += ij.col();
+  (void)count;
   a.waitLocalTiles();
   b.waitLocalTiles();
 }

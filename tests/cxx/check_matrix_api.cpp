@@ -10,6 +10,8 @@
 #include <sstream>
 #include <string>
 
+#include "dlaf/common/range2d.h"
+#include "dlaf/common/round_robin.h"
 #include "dlaf/matrix/distribution.h"
 #include "dlaf/matrix/layout_info.h"
 
@@ -25,7 +27,36 @@ static long checks = 0, failures = 0;
     }                                                                  \
   } while (0)
 
+// host-only pieces that need no table: iterate_range2d (column-major, end exclusive, empty ranges), RoundRobin
+static void check_small_utilities() {
+  const std::string where = "utilities";
+  std::string seq;
+  for (auto ij : common::iterate_range2d(LocalTileSize(3, 2)))
+    seq += std::to_string(ij.row()) + std::to_string(ij.col()) + " ";
+  EXPECT(seq == "00 10 20 01 11 21 ", where);
+  seq.clear();
+  for (auto ij : common::iterate_range2d(LocalTileIndex(1, 1), LocalTileIndex(3, 3)))
+    seq += std::to_string(ij.row()) + std::to_string(ij.col()) + " ";
+  EXPECT(seq == "11 21 12 22 ", where);
+  int n = 0;
+  for (auto ij : common::iterate_range2d(LocalTileSize(0, 5))) {
+    (void)ij;
+    ++n;
+  }
+  for (auto ij : common::iterate_range2d(LocalTileSize(4, 0))) {
+    (void)ij;
+    ++n;
+  }
+  EXPECT(n == 0, where);
+  common::RoundRobin<int> rr(3, 7);
+  EXPECT(rr.size() == 3 && rr.currentResource() == 7, where);
+  rr.nextResource() = 1;
+  rr.nextResource() = 2;
+  EXPECT(rr.nextResource() == 7 && rr.nextResource() == 1 && rr.nextResource() == 2, where);
+}
+
 int main() {
+  check_small_utilities();
   std::string line;
   while (std::getline(std::cin, line)) {
     if (line.empty())
