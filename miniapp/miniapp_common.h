@@ -1,5 +1,5 @@
 // Shared by miniapp_triangular_solver and miniapp_gen_to_std: option parsing in the reference's spelling
-// (miniapp/include/dlaf/miniapp/options.h), rank bootstrap without MPI (as miniapp_cholesky.cpp), device-side fill.
+// (miniapp/include/dlaf/miniapp/options.h), device-side fill. (Rank bootstrap: dlaf/communication/init.h.)
 #pragma once
 #include <unistd.h>
 
@@ -52,43 +52,6 @@ inline bool parse_common(int argc, char** argv, int& i, CommonOptions& o, const 
   else if (a == "--local") o.local = true;
   else return false;
   return true;
-}
-
-// One process per GPU: RANK / WORLD_SIZE / LOCAL_RANK from the launcher, NCCL id through $DLAFB_ID_FILE.
-inline void bootstrap(int& rank, int& size, const char* app) {
-  rank = std::getenv("RANK") ? std::atoi(std::getenv("RANK")) : 0;
-  size = std::getenv("WORLD_SIZE") ? std::atoi(std::getenv("WORLD_SIZE")) : 1;
-  const int local = std::getenv("LOCAL_RANK") ? std::atoi(std::getenv("LOCAL_RANK")) : rank;
-  cudaSetDevice(local);
-  unsigned char id[128] = {0};
-  const char* path = std::getenv("DLAFB_ID_FILE") ? std::getenv("DLAFB_ID_FILE") : "/tmp/dlafb_nccl_id";
-  if (size > 1) {
-    if (rank == 0) {
-      const std::string tmp = std::string(path) + ".tmp";
-      dlafb_nccl_unique_id(id);
-      FILE* f = std::fopen(tmp.c_str(), "wb");
-      std::fwrite(id, 1, 128, f);
-      std::fclose(f);
-      std::rename(tmp.c_str(), path);
-    }
-    else {
-      bool ok = false;
-      for (int tries = 0; tries < 600 && !ok; ++tries) {
-        FILE* f = std::fopen(path, "rb");
-        ok = f && std::fread(id, 1, 128, f) == 128;
-        if (f)
-          std::fclose(f);
-        if (!ok)
-          usleep(100000);
-      }
-    }
-  }
-  if (dlafb_mpi_init(rank, size, size > 1 ? id : nullptr) != 0) {
-    std::fprintf(stderr, "%s: communicator bootstrap failed\n", app);
-    std::exit(1);
-  }
-  if (size > 1 && rank == 0)
-    std::remove(path);
 }
 
 #define MINIAPP_GEN(T, CT, X)                                                                                   \

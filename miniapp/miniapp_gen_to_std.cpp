@@ -11,6 +11,8 @@
 
 #include <dlaf/eigensolver/gen_to_std.h>
 
+#include <dlaf/communication/init.h>
+
 #include "miniapp_common.h"
 
 using namespace dlaf;
@@ -92,8 +94,8 @@ static void run(const Options& opts, int rank) {
 
 int main(int argc, char** argv) {
   const Options opts = parse(argc, argv);
-  int rank = 0, size = 1;
-  miniapp::bootstrap(rank, size, "miniapp_gen_to_std");
+  dlaf::comm::mpi_init mpi_initter(argc, argv);
+  const int rank = mpi_initter.rank(), size = mpi_initter.size();
   if (opts.grid_rows * opts.grid_cols != size) {
     std::fprintf(stderr, "miniapp_gen_to_std: grid %dx%d needs %d ranks, WORLD_SIZE is %d\n", opts.grid_rows,
                  opts.grid_cols, opts.grid_rows * opts.grid_cols, size);
@@ -109,6 +111,5 @@ int main(int argc, char** argv) {
       default: std::fprintf(stderr, "unknown --type %c\n", opts.type); return 1;
     }
   }
-  dlafb_mpi_finalize();
   return 0;
 }

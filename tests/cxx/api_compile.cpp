@@ -9,6 +9,7 @@
 #include "dlaf/util_matrix.h"
 #include "dlaf/common/round_robin.h"
 #include "dlaf/common/timer.h"
+#include "dlaf/communication/init.h"
 #include "dlaf/tune.h"
 #include "dlaf/eigensolver/gen_to_std.h"
 #include "dlaf/factorization/cholesky.h"
