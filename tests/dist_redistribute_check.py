@@ -21,7 +21,8 @@ from dist_trsolve_check import to_dev  # noqa: E402
 import dlaf_oracle as orc  # noqa: E402
 
 NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
-CASES = [(37, 29, (4, 3), (8, 6)), (37, 29, (8, 6), (4, 3)), (512, 384, (32, 32), (128, 128)), (1000, 1000, (64, 64), (256, 256)),
+CASES = [(10, 10, (3, 3), (3, 3)), (10, 5, (5, 10), (10, 2)), (26, 13, (10, 3), (5, 6)),  # test_matrix.cpp:1676-1680
+         (37, 29, (4, 3), (8, 6)), (37, 29, (8, 6), (4, 3)), (512, 384, (32, 32), (128, 128)), (1000, 1000, (64, 64), (256, 256)),
          (50, 41, (5, 41), (10, 1)), (33, 70, (3, 10), (3, 10)), (1, 1, (2, 2), (4, 4)), (0, 5, (2, 2), (4, 4))]
 
 

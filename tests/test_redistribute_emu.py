@@ -5,9 +5,10 @@ memory with a size check between every pair, exchange buffers guarded.
 
 Reference semantics: matrix::copy(src, dst, grid), include/dlaf/matrix/copy.h:118-231 - same global matrix, same grid,
 the smaller block size divides the larger one in each dimension; checked against the oracle's owner lists
-(oracle/dlaf_oracle.py: local_block) - bit exact, this is byte movement. The reference's own test
-(test/unit/matrix/test_copy.cpp, MatrixCopyTest.FullMatrixCPU over sizes_tests with `sub_distributions`) uses the same
-rule: dst(i, j) == src(i, j) for every global element. GPU: tests/test_zz_redistribute_gpu.py.
+(oracle/dlaf_oracle.py: local_block) - bit exact, this is byte movement. The reference's own test of this function
+(test/unit/matrix/test_matrix.cpp:1671-1730, MatrixTest.CopyReshuffling / GPUCopyReshuffling: three size / tile
+configurations on the grids of its 6-rank environment, different source ranks for src and dst, element (i, j) = 1000 i + j,
+CHECK_MATRIX_EQ) is replayed verbatim by test_reference_reshuffling_cases. GPU: tests/test_zz_redistribute_gpu.py.
 """
 import ctypes
 import os
@@ -130,3 +131,24 @@ def test_block_sizes_that_do_not_divide_are_rejected(emu):
     a = np.zeros((10, 10))
     with pytest.raises(AssertionError):
         redistribute(emu, "d", (2, 2), "R", a, (4, 4), (0, 0), (6, 4), (0, 0))
+
+
+REF_RESHUFFLING = [((10, 10), (3, 3), (3, 3)), ((10, 5), (5, 10), (10, 2)), ((26, 13), (10, 3), (5, 6))]  # test_matrix.cpp:1676-1680
+
+
+@pytest.mark.parametrize("x", "sdcz")
+@pytest.mark.parametrize("grid,ordering", [((3, 2), "R"), ((2, 3), "C"), ((3, 1), "R"), ((1, 2), "R"), ((1, 1), "R")])
+def test_reference_reshuffling_cases(emu, x, grid, ordering):
+    """MatrixTest.CopyReshuffling: src origin (max(0, P-1), max(0, Q-1)), dst origin (min(P-1, ceil(P/2)),
+    min(Q-1, ceil(Q/2))), values 1000 i + j, exact comparison (test_matrix.cpp:1683-1712)."""
+    dt = TYPES[x]
+    P, Q = grid
+    src_origin = (max(0, P - 1), max(0, Q - 1))
+    dst_origin = (min(P - 1, -(-P // 2)), min(Q - 1, -(-Q // 2)))
+    for (m, n), st, dtile in REF_RESHUFFLING:
+        i = np.arange(m)[:, None]
+        j = np.arange(n)[None, :]
+        a = (i * 1000 + j).astype(dt)
+        out = redistribute(emu, x, grid, ordering, a, st, src_origin, dtile, dst_origin)
+        for k, (got, want) in out.items():
+            assert np.array_equal(got, want), ((m, n), st, dtile, k)
