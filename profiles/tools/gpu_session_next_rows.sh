@@ -5,6 +5,7 @@
 #   gpurun --timeout 2400 -- 'bash profiles/tools/gpu_session_next_rows.sh one'        # 1 GPU: tests, timings, ncu
 #   gpurun --gpus 2 --timeout 2400 -- 'bash profiles/tools/gpu_session_next_rows.sh two'
 #   gpurun --gpus 8 --timeout 2400 -- 'bash profiles/tools/gpu_session_next_rows.sh eight'
+#   gpurun --timeout 2400 -- 'bash profiles/tools/gpu_session_next_rows.sh sanitize'   # compute-sanitizer memcheck, small cases
 #
 # Every step is wrapped in its own `timeout` so that a hang cannot take the box with it, and continues after a
 # failure (the logs say what failed). ncu comes last and only on commands that have just exited 0 without it.
@@ -73,8 +74,16 @@ eight)
   step config4_weak8 1200 torchrun_n 8 29947 profiles/tools/bench_dist_types.py --type d --n 92160 --nb 1024
   step config4_weak8_ragged 1200 torchrun_n 8 29948 profiles/tools/bench_dist_types.py --type d --n 92682 --nb 1024 --no-check
   ;;
+sanitize)
+  # one tool per gpurun call (B200_PROFILING.md): memcheck on the smallest cases of the new code paths, and only after
+  # the same commands have exited 0 without it
+  T="tests/test_zz_redistribute_gpu.py::test_single_rank_is_a_bit_exact_copy tests/test_zz_gen_to_std_gpu.py::test_reference_known_answer tests/test_zz_triangular_dist_gpu.py::test_single_rank_grid_matches_reference_known_answer tests/test_zz_sgemm_wide_gpu.py"
+  if step sanitize_plain 900 $PY -m pytest $T -q -m gpu -x; then
+    step sanitize_memcheck 1800 compute-sanitizer --tool memcheck --error-exitcode 99 $PY -m pytest $T -q -m gpu -x
+  fi
+  ;;
 *)
-  echo "usage: $0 one|two|eight" >&2
+  echo "usage: $0 one|two|eight|sanitize" >&2
   exit 2
   ;;
 esac
