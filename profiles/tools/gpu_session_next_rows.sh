@@ -79,7 +79,7 @@ sanitize)
   # the same commands have exited 0 without it
   T="tests/test_zz_redistribute_gpu.py::test_single_rank_is_a_bit_exact_copy tests/test_zz_gen_to_std_gpu.py::test_reference_known_answer tests/test_zz_triangular_dist_gpu.py::test_single_rank_grid_matches_reference_known_answer tests/test_zz_sgemm_wide_gpu.py"
   if step sanitize_plain 900 $PY -m pytest $T -q -m gpu -x; then
-    step sanitize_memcheck 1800 compute-sanitizer --tool memcheck --error-exitcode 99 $PY -m pytest $T -q -m gpu -x
+    step sanitize_memcheck 1800 compute-sanitizer --tool memcheck --target-processes all --error-exitcode 99 $PY -m pytest $T -q -m gpu -x
   fi
   ;;
 *)
