@@ -65,6 +65,34 @@ def main():
                 if info.value != 0 or bad or not pad_ok:
                     failures.append(f"{x} {uplo} m={m} nb={nb} sub=({i0},{j0}) n={n} grid={P}x{Q} info={info.value} "
                                     f"bad={bad} pad_ok={pad_ok}")
+        # ScaLAPACK-sized blocks through dlaf_pdpotrf with the internal redistribution (DLAFB_POTRF_REDISTRIBUTE=1, read
+        # at every call): redistribute -> Cholesky at 512 -> redistribute back, distributed
+        for flag in ("1", "0"):
+            os.environ["DLAFB_POTRF_REDISTRIBUTE"] = flag
+            n, nb = 2304, 64
+            for uplo in "LU":
+                a = orc.gen_hpd(n, nb, np.float64)
+                ref = a.copy(order="F")
+                assert orc.cholesky_local(uplo, ref, nb) == 0
+                keep = (np.tril if uplo == "L" else np.triu)(np.ones((n, n))) > 0
+                full_in = np.where(keep, a, -9.9)
+                expect = np.where(keep, ref, -9.9)
+                loc, ri, ci = orc.local_block(full_in, nb, nb, (P, Q), me, src)
+                ld = max(1, loc.shape[0]) + 1
+                host = np.full((max(1, loc.shape[1]), ld), -7.7)
+                host[:loc.shape[1], :loc.shape[0]] = loc.T
+                desca = pkg.DESC9(1, ctx, n, n, nb, nb, src[0], src[1], ld)
+                info = ctypes.c_int(-1)
+                L.dlaf_pdpotrf(uplo.encode(), n, host.ctypes.data, 1, 1, desca, ctypes.byref(info))
+                got = np.ascontiguousarray(host[:loc.shape[1], :loc.shape[0]].T)
+                tol = 50 * n * float(np.finfo(np.float64).eps) * np.sqrt(2.0) * float(np.abs(ref).max())
+                bad = int(np.count_nonzero(~(np.abs(got - expect[np.ix_(ri, ci)]) <= tol))) if got.size else 0
+                pad_ok = bool(np.all(host[:loc.shape[1], loc.shape[0]:] == -7.7))
+                ncases += 1
+                if info.value != 0 or bad or not pad_ok:
+                    failures.append(f"pdpotrf nb=64 redistribute={flag} {uplo} grid={P}x{Q} info={info.value} bad={bad} "
+                                    f"pad_ok={pad_ok}")
+        os.environ["DLAFB_POTRF_REDISTRIBUTE"] = "0"
         L.dlaf_free_grid(ctx)
     L.dlaf_finalize()
     flag = torch.tensor([len(failures)], device="cuda")
