@@ -125,7 +125,44 @@ class RedistributePlan:
         pass
 
 
-pkg = types.SimpleNamespace(Grid=Grid, GenToStdPlan=GenToStdPlan, GenToStdDistPlan=GenToStdDistPlan,
+REGISTRY = {}
+
+
+def max_norm(L, grid, x, uplo, m, n, mb, nb, src, ptr, lda, stream):
+    """numpy stand-in for dlafb_max_norm (the device kernel max_abs is verified; this checks the test's expectations)."""
+    if m == 0 or n == 0:
+        return 0.0
+    a = np.frombuffer((ctypes.c_char * (n * lda * np.dtype(NP[x]).itemsize)).from_address(ptr), dtype=NP[x])
+    a = a.reshape(n, lda)[:, :m].T
+    return float(np.abs(np.tril(a) if uplo == "L" else a).max())
+
+
+class OracleCApi:
+    """dlaf_p?potrf on a host buffer through the oracle: stand-in for the C API in the sub-matrix tests."""
+
+    def __getattr__(self, name):
+        if not (name.startswith("dlaf_p") and name.endswith("potrf")):
+            raise AttributeError(name)
+        x = name[6]
+        import dlaf_oracle as orc
+
+        def potrf(uplo, n, ptr, ia, ja, desca, info_ref):
+            dt = np.dtype(NP[x])
+            m, nb, ld = desca[2], desca[4], desca[8]
+            arr = np.frombuffer((ctypes.c_char * (m * ld * dt.itemsize)).from_address(ptr), dtype=dt).reshape(m, ld)
+            i0, j0 = ia - 1, ja - 1
+            assert i0 % nb == 0 and j0 % nb == 0
+            sub = np.asfortranarray(arr[j0:j0 + n, i0:i0 + n].T.copy())
+            up = uplo.decode()
+            keep = (np.tril if up == "L" else np.triu)(np.ones((n, n))) > 0
+            work = np.asfortranarray(np.where(keep, sub, 0))
+            info_ref._obj.value = orc.cholesky_local(up, work, nb)
+            sub[keep] = work[keep]
+            arr[j0:j0 + n, i0:i0 + n] = sub.T
+        return potrf
+
+
+pkg = types.SimpleNamespace(DESC9=ctypes.c_int * 9, max_norm=max_norm, Grid=Grid, GenToStdPlan=GenToStdPlan, GenToStdDistPlan=GenToStdDistPlan,
                             TriangularSolverDistPlan=TriangularSolverDistPlan, RedistributePlan=RedistributePlan)
 
 
@@ -158,7 +195,18 @@ def main():
         assert "(2048, 2048, (512, 512), (64, 64))" in src
         red.test_single_rank_is_a_bit_exact_copy(pkg, None, x)
         ran += 1
-    print(f"dry run ok: {ran} device-test functions executed against the CPU emulation")
+    import test_zz_max_norm_gpu as nrm
+    import test_zz_submatrix_gpu as sub
+    for x in "sdcz":
+        nrm.test_max_norm_single_rank(pkg, None, x)
+        nrm.test_reference_max_norm_cases(pkg, None, x)
+        ran += 2
+    capi = OracleCApi()
+    for case in sub.CASES:
+        for uplo in "LU":
+            sub.test_pxpotrf_submatrix_host_pointer(pkg, capi, case[0], uplo, *case[1:])
+            ran += 1
+    print(f"dry run ok: {ran} device-test functions executed against the CPU emulation / numpy / oracle stand-ins")
 
 
 if __name__ == "__main__":
