@@ -16,3 +16,10 @@ def test_pending_device_tests_pass_against_the_stand_ins():
                        capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
     assert "dry run ok" in r.stdout
+
+
+def test_device_only_scripts_have_no_unbound_names():
+    """tests/check_names.py: every name loaded in a script that only runs on a GPU box is bound somewhere in it."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "check_names.py")], cwd=ROOT, capture_output=True,
+                       text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-3000:]
