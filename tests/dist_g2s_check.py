@@ -27,6 +27,7 @@ import dlaf_oracle as orc  # noqa: E402
 
 NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
 QUICK = os.environ.get("DLAFB_DIST_QUICK") == "1"
+SMALL = os.environ.get("DLAFB_CHECK_SMALL") == "1"   # CPU dry run (tests/dryrun_dist_scripts.py): same code, small sizes
 TYPES = "dz" if QUICK else "sdcz"
 
 
@@ -81,7 +82,7 @@ def main():
                     if fail:
                         failures.append(msg)
         rng = np.random.default_rng(29)
-        for x, n, nb in [("d", 1536, 128), ("d", 1100, 128), ("z", 640, 64)]:
+        for x, n, nb in ([("d", 96, 8), ("d", 69, 8), ("z", 40, 4)] if SMALL else [("d", 1536, 128), ("d", 1100, 128), ("z", 640, 64)]):
             dt = NP[x]
             cplx = x in "cz"
             g = rng.standard_normal((n, n)) + (1j * rng.standard_normal((n, n)) if cplx else 0)

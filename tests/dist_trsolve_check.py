@@ -27,6 +27,7 @@ import dlaf_oracle as orc  # noqa: E402
 
 NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
 QUICK = os.environ.get("DLAFB_DIST_QUICK") == "1"
+SMALL = os.environ.get("DLAFB_CHECK_SMALL") == "1"   # CPU dry run (tests/dryrun_dist_scripts.py): same code, small sizes
 TYPES = "dz" if QUICK else "sdcz"
 
 
@@ -92,7 +93,10 @@ def main():
                                     failures.append(msg)
         # larger random systems: aligned tiles (TMA + DMMA contractions for d and z), more tiles than ranks, ragged end
         rng = np.random.default_rng(23)
-        for x, m, n, mb, nb in [("d", 1536, 1280, 256, 128), ("d", 1100, 900, 128, 128), ("z", 640, 512, 64, 128)]:
+        big = [("d", 1536, 1280, 256, 128), ("d", 1100, 900, 128, 128), ("z", 640, 512, 64, 128)]
+        if SMALL:
+            big = [("d", 96, 80, 16, 8), ("d", 69, 57, 8, 8), ("z", 40, 32, 4, 8)]
+        for x, m, n, mb, nb in big:
             for side in "LR":
                 na = m if side == "L" else n
                 cplx = x in "cz"

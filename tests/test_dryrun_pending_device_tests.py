@@ -23,3 +23,28 @@ def test_device_only_scripts_have_no_unbound_names():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "check_names.py")], cwd=ROOT, capture_output=True,
                        text=True, timeout=120)
     assert r.returncode == 0, r.stdout[-3000:]
+
+
+import pytest  # noqa: E402
+
+
+@pytest.mark.parametrize("script", ["dist_trsolve_check", "dist_g2s_check", "dist_redistribute_check"])
+def test_multi_gpu_scripts_run_over_gloo_with_the_emulation(script):
+    """tests/dryrun_dist_scripts.py: the multi-GPU parity scripts as real two-process jobs on the CPU - gloo instead of
+    NCCL, the product's per-rank templates executed by the emulation - so that their scatter / compare / bookkeeping logic
+    is exercised before it costs a multi-GPU session."""
+    import socket
+    so = os.path.join(ROOT, "tests", "emu", "_build", "libsolver_emu.so")
+    if not os.path.exists(so):
+        subprocess.check_call(["make", "emu"], cwd=ROOT)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    env = dict(os.environ, DLAFB_CHECK_SMALL="1", DLAFB_DIST_QUICK="1")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "dryrun_dist_scripts.py"),
+                        script], cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+    tail = (r.stdout + r.stderr)[-3000:]
+    assert r.returncode == 0, tail
+    assert "total_failures=0" in r.stdout, tail
