@@ -161,7 +161,7 @@ def test_race_detector_catches_seeded_faults(emu, name):
     with open(os.path.join(mut_dir, "gen_to_std.h"), "w") as f:
         f.write(src.replace(old, new))
     so = os.path.join(mut_dir, "libsolver_emu_mut.so")
-    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O1", "-std=c++17", "-Wno-deprecated-gpu-targets", "-shared",
+    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O0", "-std=c++17", "-Wno-deprecated-gpu-targets", "-shared",
                            "-Xcompiler", "-fPIC,-pthread", "-I" + mut_dir,
                            "-I" + os.path.join(ROOT, "dla-future_b200", "csrc"),
                            "-I" + os.path.join(ROOT, "dla-future_b200", "src"), "-o", so,

@@ -157,7 +157,7 @@ def test_simulated_grid_catches_seeded_faults(emu, name):
         with open(os.path.join(mut_dir, h), "w") as f:
             f.write(text.replace(old, new) if h == fname else text)
     so = os.path.join(mut_dir, "libsolver_emu_mut.so")
-    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O1", "-std=c++17", "-Wno-deprecated-gpu-targets", "-shared",
+    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-O0", "-std=c++17", "-Wno-deprecated-gpu-targets", "-shared",
                            "-Xcompiler", "-fPIC,-pthread", "-I" + mut_dir,
                            "-I" + os.path.join(ROOT, "dla-future_b200", "csrc"),
                            "-I" + os.path.join(ROOT, "dla-future_b200", "src"), "-o", so,
