@@ -19,6 +19,7 @@ from dist_gpu_check import new_uid  # noqa: E402
 import dlaf_oracle as orc  # noqa: E402
 
 NP = {"s": np.float32, "d": np.float64, "c": np.complex64, "z": np.complex128}
+SMALL = os.environ.get("DLAFB_CHECK_SMALL") == "1"   # CPU dry run (tests/dryrun_dist_scripts.py): same code, small sizes
 
 
 def main():
@@ -36,8 +37,12 @@ def main():
         L.dlaf_create_grid_from_blacs_info(ctx, L.dlafb_mpi_comm_world(), P, Q, b"R")
         me = (rank // Q, rank % Q)
         src = (max(0, P - 1), min(1, Q - 1))
-        for x, m, nb, i0, j0, n in [("d", 1536, 128, 3, 3, 1152), ("d", 1536, 128, 2, 5, 700), ("z", 640, 64, 1, 4, 384),
-                                    ("s", 100, 8, 5, 2, 37), ("d", 64, 16, 0, 3, 16)]:
+        cases = [("d", 1536, 128, 3, 3, 1152), ("d", 1536, 128, 2, 5, 700), ("z", 640, 64, 1, 4, 384),
+                 ("s", 100, 8, 5, 2, 37), ("d", 64, 16, 0, 3, 16)]
+        if SMALL:
+            cases = [("d", 192, 16, 3, 3, 144), ("d", 192, 16, 2, 5, 87), ("z", 80, 8, 1, 4, 48), ("s", 100, 8, 5, 2, 37),
+                     ("d", 64, 16, 0, 3, 16)]
+        for x, m, nb, i0, j0, n in cases:
             for uplo in "LU":
                 dt = NP[x]
                 parent = np.full((m, m), dt(-9.9))
@@ -69,7 +74,7 @@ def main():
         # at every call): redistribute -> Cholesky at 512 -> redistribute back, distributed
         for flag in ("1", "0"):
             os.environ["DLAFB_POTRF_REDISTRIBUTE"] = flag
-            n, nb = 2304, 64
+            n, nb = (2304, 64) if not SMALL else (288, 8)
             for uplo in "LU":
                 a = orc.gen_hpd(n, nb, np.float64)
                 ref = a.copy(order="F")

@@ -162,6 +162,67 @@ def max_norm(L, grid, x, uplo, m, n, mb, nb, src, ptr, lda, stream):
     return float(t.item())
 
 
+class OracleCApi:
+    """Stand-in for the C API in tests/dist_submatrix_check.py: dlaf_p?potrf gathers the ranks' local blocks over gloo,
+    factorizes sub(A) of the global matrix with the oracle and writes every rank's part back."""
+
+    def __init__(self):
+        self.grids = {}
+
+    def dlaf_initialize(self, *a):
+        return None
+
+    def dlaf_finalize(self):
+        return None
+
+    def dlafb_mpi_init(self, rank, world, buf):
+        self.rank, self.world = rank, world
+        return 0
+
+    def dlafb_mpi_comm_world(self):
+        return None
+
+    def dlaf_create_grid_from_blacs_info(self, ctx, comm, P, Q, order):
+        self.grids[ctx] = (P, Q)
+
+    def dlaf_free_grid(self, ctx):
+        self.grids.pop(ctx, None)
+
+    def __getattr__(self, name):
+        if not (name.startswith("dlaf_p") and name.endswith("potrf")):
+            raise AttributeError(name)
+        x = name[6]
+        import dlaf_oracle as orc
+
+        def potrf(uplo, n, ptr, ia, ja, desca, info_ref):
+            dt = np.dtype(NP[x])
+            ctx, m, nb, isrc, jsrc, ld = desca[1], desca[2], desca[4], desca[6], desca[7], desca[8]
+            P, Q = self.grids[ctx]
+            me = (self.rank // Q, self.rank % Q)
+            ri = orc.local_indices(m, nb, P, me[0], isrc)
+            ci = orc.local_indices(m, nb, Q, me[1], jsrc)
+            mine = np.frombuffer((ctypes.c_char * (max(1, len(ci)) * ld * dt.itemsize)).from_address(ptr), dtype=dt)
+            mine = mine.reshape(max(1, len(ci)), ld)
+            parts = [None] * self.world
+            dist.all_gather_object(parts, (me, mine[:len(ci), :len(ri)].T.copy()))
+            glob = np.zeros((m, m), dtype=dt)
+            for (pr, pc), block in parts:
+                r2, c2 = orc.local_indices(m, nb, P, pr, isrc), orc.local_indices(m, nb, Q, pc, jsrc)
+                if r2.size and c2.size:
+                    glob[np.ix_(r2, c2)] = block
+            i0, j0 = ia - 1, ja - 1
+            assert i0 % nb == 0 and j0 % nb == 0
+            up = uplo.decode()
+            keep = (np.tril if up == "L" else np.triu)(np.ones((n, n))) > 0
+            sub = glob[i0:i0 + n, j0:j0 + n]
+            work = np.asfortranarray(np.where(keep, sub, 0))
+            info_ref._obj.value = orc.cholesky_local(up, work, nb)
+            sub[keep] = work[keep]
+            if ri.size and ci.size:
+                mine[:len(ci), :len(ri)] = glob[np.ix_(ri, ci)].T
+        return potrf
+
+
 def main():
     script = sys.argv[1]
     # ---- CPU stand-ins for what the scripts take from torch.cuda / NCCL / the device library
@@ -173,7 +234,8 @@ def main():
     torch.tensor = lambda *a, **k: real_tensor(*a, **{kk: vv for kk, vv in k.items() if kk != "device"})
     real_init = dist.init_process_group
     dist.init_process_group = lambda backend, **k: real_init("gloo")
-    pkg = types.SimpleNamespace(lib=lambda: None, Grid=Grid, TriangularSolverDistPlan=TriangularSolverDistPlan,
+    capi = OracleCApi()
+    pkg = types.SimpleNamespace(lib=lambda: capi, DESC9=ctypes.c_int * 9, Grid=Grid, TriangularSolverDistPlan=TriangularSolverDistPlan,
                                 GenToStdDistPlan=GenToStdDistPlan, RedistributePlan=RedistributePlan, max_norm=max_norm)
     import conftest
     conftest.load_package = lambda: pkg

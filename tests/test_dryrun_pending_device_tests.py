@@ -28,7 +28,7 @@ def test_device_only_scripts_have_no_unbound_names():
 import pytest  # noqa: E402
 
 
-@pytest.mark.parametrize("script", ["dist_trsolve_check", "dist_g2s_check", "dist_redistribute_check"])
+@pytest.mark.parametrize("script", ["dist_trsolve_check", "dist_g2s_check", "dist_redistribute_check", "dist_submatrix_check"])
 def test_multi_gpu_scripts_run_over_gloo_with_the_emulation(script):
     """tests/dryrun_dist_scripts.py: the multi-GPU parity scripts as real two-process jobs on the CPU - gloo instead of
     NCCL, the product's per-rank templates executed by the emulation - so that their scatter / compare / bookkeeping logic
