@@ -11,35 +11,38 @@ namespace dlaf::common {
 
 template <class T>
 class RoundRobin {
+  std::vector<T> items_;
+  std::size_t at_ = 0;  // position of the resource handed out last
+
+  void step() noexcept { at_ = at_ + 1 == items_.size() ? 0 : at_ + 1; }
+
 public:
   RoundRobin() = default;
-  /// @p n resources, each constructed from (a copy of) @p args.
-  template <class... Args>
-  RoundRobin(std::size_t n, Args... args) {
-    pool_.reserve(n);
-    for (std::size_t i = 0; i < n; ++i)
-      pool_.emplace_back(args...);
+  /// @p count resources, every one constructed from the same arguments.
+  template <class... CtorArgs>
+  explicit RoundRobin(std::size_t count, const CtorArgs&... ctor_args) {
+    items_.reserve(count);
+    while (items_.size() < count)
+      items_.emplace_back(ctor_args...);
   }
-  RoundRobin(RoundRobin&&) = default;
-  RoundRobin& operator=(RoundRobin&&) = default;
   RoundRobin(const RoundRobin&) = delete;
   RoundRobin& operator=(const RoundRobin&) = delete;
+  RoundRobin(RoundRobin&&) = default;
+  RoundRobin& operator=(RoundRobin&&) = default;
 
+  std::size_t size() const noexcept { return items_.size(); }
+
+  /// The resource handed out last (the first one before any call of nextResource).
   T& currentResource() {
-    DLAF_ASSERT(current_ < pool_.size(), current_);
-    return pool_[current_];
+    DLAF_ASSERT(!items_.empty(), items_.size());
+    return items_[at_];
   }
-  /// Advances to the next resource (wrapping around) and returns it.
+  /// Moves on to the following resource, wrapping around after the last, and returns it.
   T& nextResource() {
-    DLAF_ASSERT(!pool_.empty(), pool_.size());
-    current_ = (current_ + 1) % pool_.size();
-    return pool_[current_];
+    DLAF_ASSERT(!items_.empty(), items_.size());
+    step();
+    return items_[at_];
   }
-  std::size_t size() const noexcept { return pool_.size(); }
-
-private:
-  std::size_t current_ = 0;
-  std::vector<T> pool_;
 };
 
 }  // namespace dlaf::common
