@@ -47,6 +47,11 @@ ENGINE_API = {
     "dlafb_cholesky_plan_exchange_mode": (c_int, [c_vp]),
     "dlafb_cholesky_plan_residual": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, P_dbl, P_dbl]),
     "dlafb_launch_count": (ctypes.c_uint64, []),
+    "dlafb_capi_cached_plans": (c_int, []),
+    "dlafb_cholesky_plan_acquire": (c_int, [ctypes.POINTER(c_vp), c_vp, c_char, c_char, c_i64, c_i64, c_int, c_int]),
+    "dlafb_cholesky_plan_release": (c_int, [c_vp]),
+    "dlafb_cholesky_plan_cache_drop": (c_int, [c_vp]),
+    "dlafb_cholesky_plan_cache_size": (c_int, []),
     # include/dlafb_solver.h
     "dlafb_triangular_solver_plan_create": (c_int, [ctypes.POINTER(c_vp), c_char, c_char, c_char, c_char, c_char, c_i64,
                                                     c_i64, c_i64]),

@@ -54,21 +54,54 @@ struct PlanEntry {
   size_t dev_bytes = 0;
   int64_t ldd = 0;
   cudaStream_t stream = nullptr;
+  unsigned long long last_use = 0;
 };
 std::map<PlanKey, PlanEntry> g_plans;
+unsigned long long g_plan_clock = 0;
+
+// A plan owns streams, panel workspaces and (host-pointer callers) an n^2-byte device mirror: a caller sweeping over
+// sizes must not accumulate them. At most DLAFB_PLAN_CACHE (default 4) plans stay alive, least recently used first
+// out. Every rank of a grid issues the same sequence of factorizations, so all ranks evict the same plans.
+size_t plan_cache_limit() {
+  static const size_t v = [] {
+    const char* e = getenv("DLAFB_PLAN_CACHE");
+    const long long x = e ? atoll(e) : 4;
+    return (size_t)(x < 1 ? 1 : x);
+  }();
+  return v;
+}
 
 [[noreturn]] void die(const char* what, int code) {
   std::fprintf(stderr, "[dlaf_b200] fatal: %s (error %d)\n", what, code);
   std::abort();  // the reference's DLAF_ASSERT / *_CHECK_ERROR convention: print and terminate
 }
 
+void destroy_entry(PlanEntry& pe) {
+  dlafb_cholesky_plan_destroy(pe.plan);
+  cudaFree(pe.dev);
+  if (pe.stream)
+    cudaStreamDestroy(pe.stream);
+}
+
+void evict_lru_plans(const PlanKey& keep) {
+  while (g_plans.size() > plan_cache_limit()) {
+    auto victim = g_plans.end();
+    for (auto it = g_plans.begin(); it != g_plans.end(); ++it) {
+      const bool is_kept = !(it->first < keep) && !(keep < it->first);
+      if (!is_kept && (victim == g_plans.end() || it->second.last_use < victim->second.last_use))
+        victim = it;
+    }
+    if (victim == g_plans.end())
+      return;
+    destroy_entry(victim->second);
+    g_plans.erase(victim);
+  }
+}
+
 void drop_plans_of(int ctx) {
   for (auto it = g_plans.begin(); it != g_plans.end();) {
     if (ctx == INT_MIN || it->first.ctx == ctx) {
-      dlafb_cholesky_plan_destroy(it->second.plan);
-      cudaFree(it->second.dev);
-      if (it->second.stream)
-        cudaStreamDestroy(it->second.stream);
+      destroy_entry(it->second);
       it = g_plans.erase(it);
     }
     else
@@ -189,8 +222,10 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   if (const int nb_to = redistribution_block(d.n, d.nb))
     return cholesky_redistributed(grid, type, key.uplo, a, d.n, d.nb, sub_isrc, sub_jsrc, d.ld, nb_to);
   PlanEntry& pe = g_plans[key];
+  pe.last_use = ++g_plan_clock;
   int e;
   if (!pe.plan) {
+    evict_lru_plans(key);
     if ((e = dlafb_cholesky_plan_create(&pe.plan, grid, type, key.uplo, d.n, d.nb, sub_isrc, sub_jsrc)) != 0)
       die("plan creation failed", e);
     if (cudaStreamCreateWithFlags(&pe.stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -236,7 +271,7 @@ void pxpotrf(char type, char uplo, int n, void* a, int ia, int ja, const int des
     die("only dense ScaLAPACK descriptors (desca[0] == 1) are supported", desca[0]);
   if (ia < 1 || ja < 1)
     die("ia and ja are 1-based", ia < 1 ? ia : ja);
-  const DLAF_descriptor d = make_dlaf_descriptor(n, n, ia - 1, ja - 1, desca);
+  const DLAF_descriptor d = make_dlaf_descriptor(n, n, ia, ja, desca);
   const int r = cholesky(desca[1], type, uplo, a, d);
   if (info)
     *info = r;
@@ -245,6 +280,8 @@ void pxpotrf(char type, char uplo, int n, void* a, int ia, int ja, const int des
 }  // namespace
 
 extern "C" {
+
+int dlafb_capi_cached_plans(void) { return (int)g_plans.size(); }
 
 // ---- MPI shim ----
 MPI_Comm dlafb_mpi_comm_world(void) { return g_world; }
@@ -367,21 +404,32 @@ void dlaf_free_grid(int context) noexcept {
 }
 
 char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow, int mypcol) noexcept {
-  // src/c_api/grid.cpp:45-70 decides by all-reducing two booleans; with the rank -> coordinate maps being
-  // deterministic the local test is enough when the grid is consistent.
+  // src/c_api/grid.cpp:45-70: both tests are all-reduced (logical and) over the communicator, because rank 0 and every
+  // rank on the "diagonal" of the two numberings satisfy both; column-major wins when both hold everywhere.
   const int rank = comm ? comm->rank : 0;
-  const bool row_major = (rank == myprow * npcol + mypcol);
-  const bool col_major = (rank == mypcol * nprow + myprow);
-  if (!row_major && !col_major)
-    die("grid_ordering: coordinates match neither row- nor column-major order", rank);
-  return col_major && !row_major ? 'C' : 'R';
+  int flags[2] = {rank == myprow * npcol + mypcol ? 1 : 0, rank == mypcol * nprow + myprow ? 1 : 0};
+  if (comm && comm->size > 1) {
+    int* dev = nullptr;
+    CAPI_CUDA(cudaMalloc(&dev, sizeof(flags)), "device allocation failed");
+    CAPI_CUDA(cudaMemcpy(dev, flags, sizeof(flags), cudaMemcpyHostToDevice), "upload failed");
+    if (ncclAllReduce(dev, dev, 2, ncclInt, ncclMin, comm->world, nullptr) != ncclSuccess)
+      die("grid_ordering: all-reduce failed", -1);
+    CAPI_CUDA(cudaStreamSynchronize(nullptr), "stream synchronisation failed");
+    CAPI_CUDA(cudaMemcpy(flags, dev, sizeof(flags), cudaMemcpyDeviceToHost), "download failed");
+    cudaFree(dev);
+  }
+  if (!flags[0] && !flags[1])
+    die("grid_ordering: grid layout must be row major or column major", rank);
+  return flags[1] ? 'C' : 'R';
 }
 
 struct DLAF_descriptor make_dlaf_descriptor(const int m, const int n, const int i, const int j,
                                             const int desc[9]) noexcept {
-  if (i < 0 || j < 0)
-    die("make_dlaf_descriptor: negative sub-matrix offset", i < 0 ? i : j);
-  struct DLAF_descriptor d = {m, n, desc[4], desc[5], desc[6], desc[7], i, j, desc[8]};
+  // ScaLAPACK's 1-based (ia, ja), stored 0-based like the reference does (src/c_api/utils.cpp:25-33). The reference
+  // asserts i == j == 1; this build goes on to accept tile-aligned sub-matrices (checked where they are used).
+  if (i < 1 || j < 1)
+    die("make_dlaf_descriptor: i and j are 1-based (ScaLAPACK ia, ja)", i < 1 ? i : j);
+  struct DLAF_descriptor d = {m, n, desc[4], desc[5], desc[6], desc[7], i - 1, j - 1, desc[8]};
   return d;
 }
 

@@ -218,6 +218,7 @@ struct Plan final : dlafb_chol_plan {
   int2* lists = nullptr;
   std::vector<size_t> hp_off, np_off;
   int* info_dev = nullptr;
+  int* info_red = nullptr;  // grid-wide reduction of info
   T* tbuf = nullptr;  // transposed local block (Upper) or aligned mirror
   int64_t ldt = 0;
   // profiling of the bulk (np stream) update launches: one timed event pair per step
@@ -276,6 +277,7 @@ struct Plan final : dlafb_chol_plan {
     cudaFree(rlists);
     cudaFree(r_out);
     cudaFree(info_dev);
+    cudaFree(info_red);
     cudaFree(tbuf);
     for (cudaEvent_t e : pev)
       cudaEventDestroy(e);
@@ -1214,6 +1216,10 @@ struct Plan final : dlafb_chol_plan {
     CU(cudaEventRecord(ev_in, user));
     CU(cudaStreamWaitEvent(hp, ev_in, 0));
     CU(cudaStreamWaitEvent(np, ev_in, 0));
+    // a plan may be reused from another caller stream before the previous run has drained (cached plans of the C++
+    // API): each of the two streams also waits for the other one's end of the previous run (no-ops the first time)
+    CU(cudaStreamWaitEvent(hp, ev_np_end, 0));
+    CU(cudaStreamWaitEvent(np, ev_hp_end, 0));
     CU(cudaMemsetAsync(info_dev, 0, sizeof(int), hp));
     int r = 0;
     if (n > 0) {
@@ -1259,6 +1265,19 @@ struct Plan final : dlafb_chol_plan {
     CU(cudaStreamSynchronize(np));
     int v = 0;
     CU(cudaMemcpy(&v, info_dev, sizeof(int), cudaMemcpyDeviceToHost));
+    if (dist) {
+      // ScaLAPACK convention: the same info on every rank. The kernel sets it only where the failing diagonal tile
+      // lives: take the smallest non-zero value over the grid (first failing column). Collective, like the run.
+      if (!info_red)
+        CU(cudaMalloc(&info_red, sizeof(int)));
+      const int mine = v != 0 ? v : 0x7fffffff;
+      CU(cudaMemcpyAsync(info_red, &mine, sizeof(int), cudaMemcpyHostToDevice, hp));
+      NC(ncclAllReduce(info_red, info_red, 1, ncclInt, ncclMin, worldc, hp));
+      CU(cudaMemcpyAsync(&v, info_red, sizeof(int), cudaMemcpyDeviceToHost, hp));
+      CU(cudaStreamSynchronize(hp));
+      if (v == 0x7fffffff)
+        v = 0;
+    }
     *out = v;
     return 0;
   }
@@ -1297,8 +1316,15 @@ int dlafb_cholesky_plan_create(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char 
 
 int dlafb_cholesky_plan_run_host(dlafb_chol_plan_t plan, void* host, int64_t ldh, void* dev, int64_t ldd,
                                  void* stream) {
-  if (!plan || !host || !dev)
+  if (!plan || !dev)
     return 1;
+  if (!host) {
+    // a rank whose local block is empty may pass NULL (ScaLAPACK callers do): it still takes part in the exchange
+    int64_t r = 0, c = 0;
+    plan->local_size(&r, &c);
+    if (r > 0 && c > 0)
+      return 1;
+  }
   return plan->run_host(host, ldh, dev, ldd, static_cast<cudaStream_t>(stream));
 }
 
@@ -1352,6 +1378,91 @@ int dlafb_cholesky_plan_destroy(dlafb_chol_plan_t plan) {
   delete plan;
   return 0;
 }
+
+// ---- plans kept alive between calls (the C++ front end: plan creation is a collective with allocations, IPC
+//      mappings and list uploads; destruction synchronises the device). At most kPlanCacheLimit idle plans stay;
+//      a plan that is in use (acquired, not yet released) is never destroyed. Every rank of a grid makes the same
+//      sequence of calls, so all ranks keep and drop the same plans. ----
+namespace {
+struct CachedPlan {
+  dlafb_grid_t grid;
+  char type, uplo;
+  int64_t n, nb;
+  int sr, sc;
+  dlafb_chol_plan_t plan;
+  int refs;
+  unsigned long long last_use;
+};
+std::vector<CachedPlan>& plan_cache() {
+  static std::vector<CachedPlan>* v = new std::vector<CachedPlan>();  // never destroyed: no CUDA calls at exit
+  return *v;
+}
+unsigned long long g_cache_clock = 0;
+constexpr size_t kPlanCacheLimit = 4;
+void cache_trim() {
+  auto& v = plan_cache();
+  while (v.size() > kPlanCacheLimit) {
+    size_t lru = v.size();
+    for (size_t i = 0; i < v.size(); ++i)
+      if (v[i].refs == 0 && (lru == v.size() || v[i].last_use < v[lru].last_use))
+        lru = i;
+    if (lru == v.size())
+      return;  // everything is in use
+    delete v[lru].plan;
+    v.erase(v.begin() + (long)lru);
+  }
+}
+}  // namespace
+
+int dlafb_cholesky_plan_acquire(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char type, char uplo, int64_t n, int64_t nb,
+                                int src_r, int src_c) {
+  if (!plan || !grid)
+    return -1;
+  uplo = (uplo == 'u' || uplo == 'U') ? 'U' : 'L';
+  auto& v = plan_cache();
+  for (CachedPlan& c : v)
+    if (c.grid == grid && c.type == type && c.uplo == uplo && c.n == n && c.nb == nb && c.sr == src_r &&
+        c.sc == src_c) {
+      ++c.refs;
+      c.last_use = ++g_cache_clock;
+      *plan = c.plan;
+      return 0;
+    }
+  dlafb_chol_plan_t p = nullptr;
+  const int e = dlafb_cholesky_plan_create(&p, grid, type, uplo, n, nb, src_r, src_c);
+  if (e != 0)
+    return e;
+  v.push_back(CachedPlan{grid, type, uplo, n, nb, src_r, src_c, p, 1, ++g_cache_clock});
+  cache_trim();
+  *plan = p;
+  return 0;
+}
+
+int dlafb_cholesky_plan_release(dlafb_chol_plan_t plan) {
+  for (CachedPlan& c : plan_cache())
+    if (c.plan == plan) {
+      if (c.refs > 0)
+        --c.refs;
+      cache_trim();
+      return 0;
+    }
+  return -1;
+}
+
+int dlafb_cholesky_plan_cache_drop(dlafb_grid_t grid) {
+  auto& v = plan_cache();
+  for (size_t i = 0; i < v.size();) {
+    if (grid == nullptr || v[i].grid == grid) {
+      delete v[i].plan;  // the grid goes: its plans cannot run any more
+      v.erase(v.begin() + (long)i);
+    }
+    else
+      ++i;
+  }
+  return 0;
+}
+
+int dlafb_cholesky_plan_cache_size(void) { return (int)plan_cache().size(); }
 
 int dlafb_cholesky_plan_local_size(dlafb_chol_plan_t plan, int64_t* rows, int64_t* cols) {
   if (!plan || !rows || !cols)

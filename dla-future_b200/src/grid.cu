@@ -101,6 +101,7 @@ int dlafb_grid_create_local(dlafb_grid_t* out) {
 int dlafb_grid_destroy(dlafb_grid_t g) {
   if (!g)
     return 0;
+  dlafb_cholesky_plan_cache_drop(g);  // cached plans hold this grid's communicators
   if (g->row)
     ncclCommDestroy(g->row);
   if (g->col)

@@ -22,12 +22,14 @@ struct Cholesky {
 
   static void call(dlafb_grid_t grid, blas::Uplo uplo, Matrix<T, device>& mat_a) {
     const matrix::Distribution& d = mat_a.distribution();
+    // the library keeps the plan for (grid, type, uplo, size, block size, source rank) between calls: creating one is a
+    // collective with allocations and peer mappings, destroying one synchronises the device
     dlafb_chol_plan_t plan = nullptr;
-    int e = dlafb_cholesky_plan_create(&plan, grid, dlaf::internal::TypeCode<T>::value, static_cast<char>(uplo),
-                                       d.size().rows(), d.block_size().rows(), d.source_rank_index().row(),
-                                       d.source_rank_index().col());
+    int e = dlafb_cholesky_plan_acquire(&plan, grid, dlaf::internal::TypeCode<T>::value, static_cast<char>(uplo),
+                                        d.size().rows(), d.block_size().rows(), d.source_rank_index().row(),
+                                        d.source_rank_index().col());
     DLAF_ASSERT(e == 0, e);
-    std::shared_ptr<void> keep(plan, [](void* p) { dlafb_cholesky_plan_destroy(static_cast<dlafb_chol_plan_t>(p)); });
+    std::shared_ptr<void> keep(plan, [](void* p) { dlafb_cholesky_plan_release(static_cast<dlafb_chol_plan_t>(p)); });
     e = dlafb_cholesky_plan_run(plan, mat_a.ptr(), mat_a.ld(), mat_a.stream());
     DLAF_ASSERT(e == 0, e);
     mat_a.keep_alive(keep, [plan] {

@@ -21,7 +21,8 @@ typedef double complex dlaf_complex_z;
 
 #include <dlaf_c/desc.h>
 
-/* ScaLAPACK descriptor (desc[0] == 1 dense) -> DLAF descriptor; i, j are 0-based here (reference:
- * src/c_api/utils.cpp:25-33). */
+/* ScaLAPACK descriptor (desc[0] == 1 dense) -> DLAF descriptor. i, j are ScaLAPACK's 1-based (ia, ja) and are
+ * stored 0-based in the result, exactly as the reference does (src/c_api/utils.cpp:25-33, which stops at
+ * i == j == 1; here any i, j >= 1 whose 0-based value is a multiple of the block size is accepted downstream). */
 DLAF_EXTERN_C struct DLAF_descriptor make_dlaf_descriptor(const int m, const int n, const int i, const int j,
                                                           const int desc[9]) DLAF_NOEXCEPT;

@@ -79,9 +79,20 @@ int dlafb_cholesky_plan_run(dlafb_chol_plan_t plan, void* a, int64_t lda, void* 
  * steps. Asynchronous on `stream`; `host` should be pinned for the copies to overlap. */
 int dlafb_cholesky_plan_run_host(dlafb_chol_plan_t plan, void* host, int64_t ldh, void* dev, int64_t ldd, void* stream);
 /* Synchronises with the last run and returns its info: 0, or the 1-based global column of the first
- * non-positive pivot (ScaLAPACK p?potrf convention). */
+ * non-positive pivot (ScaLAPACK p?potrf convention: the same value on every rank, so on a grid this call is
+ * collective - one small all-reduce). */
 int dlafb_cholesky_plan_info(dlafb_chol_plan_t plan, int* info);
 int dlafb_cholesky_plan_destroy(dlafb_chol_plan_t plan);
+/* Cached plans (what the C++ front end uses: creating a plan is a collective with allocations and peer mappings,
+ * destroying one synchronises the device). `acquire` returns the plan the library keeps for (grid, type, uplo, n,
+ * nb, source rank), creating it on first use; `release` says the caller is done with it (after the run has been
+ * waited for). Idle plans beyond a small limit are destroyed least recently used first; `cache_drop(grid)` destroys
+ * the plans of one grid (dlafb_grid_destroy calls it), `cache_drop(NULL)` all of them. Collective like create. */
+int dlafb_cholesky_plan_acquire(dlafb_chol_plan_t* plan, dlafb_grid_t grid, char type, char uplo, int64_t n, int64_t nb,
+                                int src_r, int src_c);
+int dlafb_cholesky_plan_release(dlafb_chol_plan_t plan);
+int dlafb_cholesky_plan_cache_drop(dlafb_grid_t grid);
+int dlafb_cholesky_plan_cache_size(void);
 /* Local block dimensions of this rank for the plan's matrix. */
 int dlafb_cholesky_plan_local_size(dlafb_chol_plan_t plan, int64_t* rows, int64_t* cols);
 
@@ -106,6 +117,10 @@ int dlafb_cholesky_plan_residual(dlafb_chol_plan_t plan, void* a0, int64_t lda, 
  * 2 = copies into the peers' memory over NVLink (CUDA IPC, copy engines) with stream-ordered step counters; chosen at
  * plan creation (2 when every rank of the grid can map its row and column peers; DLAFB_P2P=0 forces 1). */
 int dlafb_cholesky_plan_exchange_mode(dlafb_chol_plan_t plan);
+
+/* Factorization plans the reference-facing C API (include/dlaf_c) currently keeps alive: at most DLAFB_PLAN_CACHE
+ * (default 4), least recently used first out. */
+int dlafb_capi_cached_plans(void);
 
 /* Kernels launched by this library so far in this process. */
 uint64_t dlafb_launch_count(void);

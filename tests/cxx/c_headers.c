@@ -35,7 +35,7 @@ any_fn c_api_symbols[] = {
 int use_descriptor(void) {
   struct DLAF_descriptor d = {8, 8, 4, 4, 0, 0, 0, 0, 8};
   int desca[9] = {1, 0, 8, 8, 4, 4, 0, 0, 8};
-  struct DLAF_descriptor e = make_dlaf_descriptor(8, 8, 4, 4, desca);
+  struct DLAF_descriptor e = make_dlaf_descriptor(8, 8, 5, 5, desca) /* 1-based ia, ja: sub-matrix at tile (1, 1) */;
   return d.m + e.i;
 }
 

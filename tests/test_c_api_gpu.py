@@ -112,3 +112,74 @@ def test_pdpotrf_not_positive_definite_info(pkg, capi):
     info = ctypes.c_int(0)
     L.dlaf_pdpotrf(b"L", n, h.ctypes.data, 1, 1, desca, ctypes.byref(info))
     assert info.value == 301
+
+
+def test_make_dlaf_descriptor_is_one_based_like_the_reference(pkg, capi):
+    """A caller ported from the reference: make_dlaf_descriptor(n, n, 1, 1, desca) (ScaLAPACK ia = ja = 1, stored
+    0-based: src/c_api/utils.cpp:25-33) followed by dlaf_cholesky_factorization_d."""
+    L = capi
+    n, nb = 384, 128
+    a, t = orc.cholesky_setters(n, "L", np.float64)
+    h = host_colmajor(a, n, 0.0)
+    desca = pkg.DESC9(1, CTX, n, n, nb, nb, 0, 0, n)
+    d = L.make_dlaf_descriptor(n, n, 1, 1, desca)
+    assert (d.m, d.n, d.mb, d.nb, d.isrc, d.jsrc, d.i, d.j, d.ld) == (n, n, nb, nb, 0, 0, 0, 0, n)
+    assert L.dlaf_cholesky_factorization_d(CTX, b"L", h.ctypes.data, d) == 0
+    got = np.ascontiguousarray(h[:n, :n].T)
+    tol = 4 * (n + 1) * orc.type_error(np.float64)
+    assert orc.check_near(np.tril(got), np.tril(t), tol, tol) == 0
+    # tile-aligned sub-matrix through the same 1-based arguments
+    e = L.make_dlaf_descriptor(n - nb, n - nb, nb + 1, nb + 1, desca)
+    assert (e.i, e.j) == (nb, nb)
+
+
+def test_plan_cache_of_the_c_api_is_bounded(pkg, capi):
+    """A caller sweeping over sizes must not accumulate plans and n^2-byte device mirrors (LRU, DLAFB_PLAN_CACHE = 4)."""
+    L = capi
+    for n in (128, 192, 256, 320, 384, 448, 512):
+        a, t = orc.cholesky_setters(n, "L", np.float64)
+        h = host_colmajor(a, n, 0.0)
+        desca = pkg.DESC9(1, CTX, n, n, 64, 64, 0, 0, n)
+        info = ctypes.c_int(-1)
+        L.dlaf_pdpotrf(b"L", n, h.ctypes.data, 1, 1, desca, ctypes.byref(info))
+        assert info.value == 0
+        tol = 4 * (n + 1) * orc.type_error(np.float64)
+        assert orc.check_near(np.tril(np.ascontiguousarray(h[:n, :n].T)), np.tril(t), tol, tol) == 0
+        assert L.dlafb_capi_cached_plans() <= 4
+    # an evicted size is simply rebuilt
+    n = 128
+    a, t = orc.cholesky_setters(n, "L", np.float64)
+    h = host_colmajor(a, n, 0.0)
+    desca = pkg.DESC9(1, CTX, n, n, 64, 64, 0, 0, n)
+    info = ctypes.c_int(-1)
+    L.dlaf_pdpotrf(b"L", n, h.ctypes.data, 1, 1, desca, ctypes.byref(info))
+    assert info.value == 0 and L.dlafb_capi_cached_plans() <= 4
+
+
+def test_cached_plans_of_the_engine(pkg, L):
+    """dlafb_cholesky_plan_acquire / release (what dlaf::cholesky_factorization<> uses): the same plan comes back for
+    the same key, idle plans beyond the limit go, a grid's plans go with the grid."""
+    grid = pkg.Grid(L)
+    p1, p2 = ctypes.c_void_p(), ctypes.c_void_p()
+    base = L.dlafb_cholesky_plan_cache_size()
+    pkg.check(L.dlafb_cholesky_plan_acquire(ctypes.byref(p1), grid.h, b"d", b"L", 256, 64, 0, 0), "acquire")
+    pkg.check(L.dlafb_cholesky_plan_release(p1), "release")
+    pkg.check(L.dlafb_cholesky_plan_acquire(ctypes.byref(p2), grid.h, b"d", b"L", 256, 64, 0, 0), "acquire")
+    assert p1.value == p2.value and L.dlafb_cholesky_plan_cache_size() == base + 1
+    a, t = orc.cholesky_setters(256, "L", np.float64)
+    A = DevMat(a)
+    pkg.check(L.dlafb_cholesky_plan_run(p2, A.ptr, A.ld, None), "run")
+    info = ctypes.c_int(-1)
+    pkg.check(L.dlafb_cholesky_plan_info(p2, ctypes.byref(info)), "info")
+    sync()
+    assert info.value == 0
+    tol = 4 * 257 * orc.type_error(np.float64)
+    assert orc.check_near(np.tril(A.get()), np.tril(t), tol, tol) == 0
+    pkg.check(L.dlafb_cholesky_plan_release(p2), "release")
+    for n in (64, 128, 192, 320, 384, 448):
+        q = ctypes.c_void_p()
+        pkg.check(L.dlafb_cholesky_plan_acquire(ctypes.byref(q), grid.h, b"d", b"L", n, 64, 0, 0), "acquire")
+        pkg.check(L.dlafb_cholesky_plan_release(q), "release")
+        assert L.dlafb_cholesky_plan_cache_size() <= 4
+    grid.close()
+    assert L.dlafb_cholesky_plan_cache_size() <= base
