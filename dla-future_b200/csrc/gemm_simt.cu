@@ -25,11 +25,11 @@ __global__ void __launch_bounds__(kWideThreads, 2) gemm_simt_wide_kernel(const S
   gemm_simt_wide_body(p, c);
 }
 
-// DLAFB_SGEMM_WIDE=1 routes float contractions to the 128 x 128 kernel (read once).
+// float contractions run on the 128 x 128 kernel; DLAFB_SGEMM_WIDE=0 keeps the 64 x 64 one (read once).
 bool wide_enabled() {
   static const bool on = [] {
     const char* e = getenv("DLAFB_SGEMM_WIDE");
-    return e && e[0] == '1';
+    return !(e && e[0] == '0');
   }();
   return on;
 }

@@ -7,7 +7,8 @@
 //
 // The body is a __host__ __device__ function of a context object (thread / block indices, the two shared-memory
 // slices, the barrier), so that tests/emu/ runs exactly this code on the CPU with one host thread per CUDA thread of a
-// block. Selected by DLAFB_SGEMM_WIDE=1 (off until it has been run and timed on the device: DESIGN.md section 15).
+// block. The default for float since round 2 (38.2 vs 27.5 TFLOP/s for the n = 32768 factorization with the single-buffered
+// first version, profiles/r02/session1_summary.txt); DLAFB_SGEMM_WIDE=0 selects the 64 x 64 kernel.
 #pragma once
 #include "gemm_simt.cuh"
 
@@ -24,7 +25,7 @@ constexpr int kWideTile = 128;           // C block per CTA
 constexpr int kWideSK = 8;               // K-slice
 constexpr int kWideLd = kWideTile + 4;   // row stride of a slice in shared memory (floats); keeps 16-byte alignment
 constexpr int kWideThreads = 256;
-constexpr int kWideSmemFloats = 2 * kWideSK * kWideLd;  // A slice + B slice
+constexpr int kWideSmemFloats = 2 * 2 * kWideSK * kWideLd;  // two buffers of (A slice + B slice)
 
 // Context on the device: see gemm_simt.cu. Context on the host: tests/emu/simt_wide_emu.cu.
 //   int tid(), bx(), by();  float* smem();  void sync();
@@ -65,8 +66,11 @@ __host__ __device__ inline void gemm_simt_wide_body(const SimtParams<float>& p, 
   if (lower && trow + TILE - 1 < tcol)
     return;
 
-  float* As = c.smem();            // [SK][LD]
-  float* Bs = As + SK * LD;        // [SK][LD]
+  // two buffers of [A slice | B slice], each slice [SK][LD]: the next slice is written into the buffer that was read in
+  // the previous iteration, so one barrier per slice is enough
+  float* As = c.smem();
+  float* Bs = As + SK * LD;
+  constexpr int BUF = 2 * SK * LD;
   const int tid = c.tid();
   const int tx = tid & 15, ty = tid >> 4;
   const int lr = tid & (TILE - 1);  // loader: row inside the block
@@ -100,28 +104,31 @@ DLAFB_WIDE_UNROLL
       pb[h] = (b_ok && k < p.K) ? bp[(long long)k * ldb] : 0.f;
     }
   };
-  auto stash = [&]() {
+  auto stash = [&](int buf) {
 DLAFB_WIDE_UNROLL
     for (int h = 0; h < 4; ++h) {
-      As[(lk + 2 * h) * LD + lr] = pa[h];
-      Bs[(lk + 2 * h) * LD + lr] = pb[h];
+      As[buf * BUF + (lk + 2 * h) * LD + lr] = pa[h];
+      Bs[buf * BUF + (lk + 2 * h) * LD + lr] = pb[h];
     }
   };
 
   fetch(0);
-  stash();
+  stash(0);
   c.sync();
+  int cur = 0;
   for (int k0 = 0; k0 < p.K; k0 += SK) {
     const bool more = k0 + SK < p.K;
     if (more)
       fetch(k0 + SK);  // global loads in flight during the multiplication below
+    const float* Ac = As + cur * BUF;
+    const float* Bc = Bs + cur * BUF;
 DLAFB_WIDE_UNROLL
     for (int k = 0; k < SK; ++k) {
       // rows 4 tx + {0..3} and 64 + 4 tx + {0..3}; columns 4 ty + {0..3} and 64 + 4 ty + {0..3}
-      const float4 a0 = *reinterpret_cast<const float4*>(As + k * LD + 4 * tx);
-      const float4 a1 = *reinterpret_cast<const float4*>(As + k * LD + 64 + 4 * tx);
-      const float4 b0 = *reinterpret_cast<const float4*>(Bs + k * LD + 4 * ty);
-      const float4 b1 = *reinterpret_cast<const float4*>(Bs + k * LD + 64 + 4 * ty);
+      const float4 a0 = *reinterpret_cast<const float4*>(Ac + k * LD + 4 * tx);
+      const float4 a1 = *reinterpret_cast<const float4*>(Ac + k * LD + 64 + 4 * tx);
+      const float4 b0 = *reinterpret_cast<const float4*>(Bc + k * LD + 4 * ty);
+      const float4 b1 = *reinterpret_cast<const float4*>(Bc + k * LD + 64 + 4 * ty);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
       const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 DLAFB_WIDE_UNROLL
@@ -130,11 +137,10 @@ DLAFB_WIDE_UNROLL
         for (int j = 0; j < 8; ++j)
           acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
-    c.sync();  // everyone is done reading the slice
-    if (more) {
-      stash();
-      c.sync();
-    }
+    if (more)
+      stash(cur ^ 1);  // the buffer everyone finished reading before the previous barrier
+    c.sync();
+    cur ^= 1;
   }
 
   const float alpha = p.alpha, beta = p.beta;

@@ -21,8 +21,9 @@ struct TuneParameters {
   /// DLAFB_G2S_LOOKAHEAD: two-stream look-ahead variant of the one-GPU generalized-to-standard reduction. Read at plan
   /// creation.
   int gen_to_std_lookahead = env_int("DLAFB_G2S_LOOKAHEAD", 0);
-  /// DLAFB_SGEMM_WIDE [process]: float contractions on the 128x128 kernel (off until timed on the device).
-  int sgemm_wide = env_int("DLAFB_SGEMM_WIDE", 0);
+  /// DLAFB_SGEMM_WIDE [process]: float contractions on the 128x128 kernel (default since it was timed: 38 vs 27 TFLOP/s
+  /// for the n = 32768 factorization); 0 selects the 64x64 kernel.
+  int sgemm_wide = env_int("DLAFB_SGEMM_WIDE", 1);
   /// DLAFB_POTRF_REDISTRIBUTE: dlaf_p?potrf redistributes matrices with block sizes below 256 to <= 512, factorizes and
   /// redistributes back. Read at every call.
   int potrf_redistribute = env_int("DLAFB_POTRF_REDISTRIBUTE", 0);
