@@ -177,8 +177,8 @@ struct Plan final : dlafb_chol_plan {
   // the group's own stream, which waits for that group's upload only.
   static constexpr int kUpGroups = 8;
   cudaStream_t uh = nullptr, gs[kUpGroups] = {};
-  cudaEvent_t ev_up[kUpGroups] = {}, ev_grp[kUpGroups] = {};
-  std::vector<int> grp_of_col;                 // local tile column -> upload group
+  cudaEvent_t ev_up[kUpGroups] = {}, ev_grp[2][kUpGroups] = {};  // ev_grp[step parity][group]
+  std::vector<int> grp_of_col;                 // LOCAL tile column -> upload group
   std::vector<size_t> split_off;               // [step * (kUpGroups + 1) + g]: range in lists_split
   int2* lists_split = nullptr;
   int64_t up_steps = 0;                        // steps with a split bulk update (0: no overlap possible)
@@ -242,7 +242,8 @@ struct Plan final : dlafb_chol_plan {
     for (int g = 0; g < kUpGroups; ++g) {
       if (gs[g]) cudaStreamDestroy(gs[g]);
       if (ev_up[g]) cudaEventDestroy(ev_up[g]);
-      if (ev_grp[g]) cudaEventDestroy(ev_grp[g]);
+      if (ev_grp[0][g]) cudaEventDestroy(ev_grp[0][g]);
+      if (ev_grp[1][g]) cudaEventDestroy(ev_grp[1][g]);
     }
     cudaFree(lists_split);
     if (ev_col) cudaEventDestroy(ev_col);
@@ -574,19 +575,24 @@ struct Plan final : dlafb_chol_plan {
       CU(cudaMalloc(&lists, all.size() * sizeof(int2)));
       CU(cudaMemcpy(lists, all.data(), all.size() * sizeof(int2), cudaMemcpyHostToDevice));
     }
-    if (!dist && !upper && nt >= 16) {
-      // upload groups of growing size
-      grp_of_col.assign((size_t)nt, 0);
+    const int64_t ctl = sched.cols.nloc_tiles();
+    if (!upper && nt >= 16 && ctl >= 4 && mloc > 0) {
+      // upload groups of growing size over the LOCAL tile columns (single rank: local = global)
+      grp_of_col.assign((size_t)ctl, 0);
+      auto weight = [&](int64_t jl) {
+        const int64_t gj = sched.cols.global_of(jl);
+        return (double)(mloc - sched.rows.next_local(gj) * nb) * (double)sched.cols.tile_size(gj);
+      };
       double total = 0, acc = 0;
-      for (int64_t j = 0; j < nt; ++j)
-        total += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
-      for (int64_t j = 0; j < nt; ++j) {
+      for (int64_t jl = 0; jl < ctl; ++jl)
+        total += weight(jl);
+      for (int64_t jl = 0; jl < ctl; ++jl) {
         // group g ends at the fraction ((g+1)/G)^2 of the bytes: small first groups start the factorization early
-        grp_of_col[(size_t)j] = std::min<int>(kUpGroups - 1, (int)(std::sqrt(acc / total) * kUpGroups));
-        acc += (double)(n - j * nb) * (double)sched.cols.tile_size(j);
+        grp_of_col[(size_t)jl] = total > 0 ? std::min<int>(kUpGroups - 1, (int)(std::sqrt(acc / total) * kUpGroups)) : 0;
+        acc += weight(jl);
       }
       const char* ue = getenv("DLAFB_UP_STEPS");
-      up_steps = std::min<int64_t>(ue ? atoll(ue) : 10, nt - 2);
+      up_steps = std::min<int64_t>(ue ? atoll(ue) : (dist ? 16 : 10), nt - 2);
       std::vector<int2> sp;
       split_off.assign((size_t)up_steps * (kUpGroups + 1), 0);
       for (int64_t k = 0; k < up_steps; ++k)
@@ -605,7 +611,8 @@ struct Plan final : dlafb_chol_plan {
       for (int g = 0; g < kUpGroups; ++g) {
         CU(cudaStreamCreateWithPriority(&gs[g], cudaStreamNonBlocking, lo));
         CU(cudaEventCreateWithFlags(&ev_up[g], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&ev_grp[g], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ev_grp[0][g], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ev_grp[1][g], cudaEventDisableTiming));
       }
     }
     np_flops.assign(nt + 1, 0.0);
@@ -942,11 +949,23 @@ struct Plan final : dlafb_chol_plan {
       const bool mark = profiling && !last;
       if (mark)
         CU(cudaEventRecord(hev[6 * k + 0], hp));
+      // upload group of global tile column g on this rank, -1 when another grid column owns it
+      auto col_group = [&](int64_t g) -> int {
+        if (g >= nt || sched.cols.owner(g) != pc)
+          return -1;
+        return grp_of_col[(size_t)sched.cols.local_of(g)];
+      };
       if (up_on) {
         // tile column k (and k+1 for the look-ahead update) must have arrived from the host
-        CU(cudaStreamWaitEvent(hp, ev_up[grp_of_col[(size_t)k]], 0));
-        if (!last)
-          CU(cudaStreamWaitEvent(hp, ev_up[grp_of_col[(size_t)(k + 1)]], 0));
+        const int g0 = col_group(k), g1 = last ? -1 : col_group(k + 1);
+        if (g0 >= 0)
+          CU(cudaStreamWaitEvent(hp, ev_up[g0], 0));
+        if (g1 >= 0)
+          CU(cudaStreamWaitEvent(hp, ev_up[g1], 0));
+        // distributed: the split bulk update of step k-2 read the panel buffers this step is about to overwrite
+        if (dist && k >= 2 && k <= up_steps + 1)
+          for (int g = 0; g < kUpGroups; ++g)
+            CU(cudaStreamWaitEvent(hp, ev_grp[k & 1][g], 0));
       }
       if (st.own_diag) {
         Akk = A + (size_t)st.lk_row * nb + (size_t)st.lk_col * nb * ld;
@@ -1103,8 +1122,11 @@ struct Plan final : dlafb_chol_plan {
         }
         CU(cudaEventRecord(ev_panel[buf], hp));
         // look-ahead: global column k+1 on the high-priority stream, after np(k-1) which touched it last
-        if (k >= 1 && up_on && k - 1 < up_steps)
-          CU(cudaStreamWaitEvent(hp, ev_grp[grp_of_col[(size_t)(k + 1)]], 0));  // split bulk update of step k-1
+        if (k >= 1 && up_on && k - 1 < up_steps) {
+          const int g1 = col_group(k + 1);
+          if (g1 >= 0)
+            CU(cudaStreamWaitEvent(hp, ev_grp[(k - 1) & 1][g1], 0));  // split bulk update of step k-1
+        }
         else if (k >= 1)
           CU(cudaStreamWaitEvent(hp, ev_np[(k - 1) & 1], 0));
         int r = 0;
@@ -1124,42 +1146,48 @@ struct Plan final : dlafb_chol_plan {
           return r;
         if (mark)
           CU(cudaEventRecord(hev[6 * k + 5], hp));
-        if (up_on && k < up_steps) {
+        const bool split = up_on && k < up_steps;
+        if (split) {
           // one launch per upload group on the group's stream: the groups that have arrived run ahead
           for (int g = 0; g < kUpGroups; ++g) {
             const size_t o = split_off[(size_t)k * (kUpGroups + 1) + g];
             const size_t c = split_off[(size_t)k * (kUpGroups + 1) + g + 1] - o;
-            if (c == 0)
-              continue;
-            if (k == 0)
-              CU(cudaStreamWaitEvent(gs[g], ev_in, 0));
-            CU(cudaStreamWaitEvent(gs[g], ev_up[g], 0));
-            CU(cudaStreamWaitEvent(gs[g], ev_panel[buf], 0));
-            r = update(gs[g], A, ld, map_local, nbox_local, k, buf, o, c, true, lists_split);
-            if (r != 0)
-              return r;
-            CU(cudaEventRecord(ev_grp[g], gs[g]));
+            if (c > 0) {
+              if (k == 0)
+                CU(cudaStreamWaitEvent(gs[g], ev_in, 0));
+              CU(cudaStreamWaitEvent(gs[g], ev_up[g], 0));
+              CU(cudaStreamWaitEvent(gs[g], ev_panel[buf], 0));
+              r = update(gs[g], A, ld, map_local, nbox_local, k, buf, o, c, true, lists_split);
+              if (r != 0)
+                return r;
+            }
+            CU(cudaEventRecord(ev_grp[buf][g], gs[g]));
           }
           np_timed[k] = 0;
-          continue;
         }
-        if (up_on && k == up_steps)
-          for (int g = 0; g < kUpGroups; ++g) {  // join: from here on one launch per step again
-            CU(cudaStreamWaitEvent(np, ev_grp[g], 0));
-            CU(cudaStreamWaitEvent(np, ev_up[g], 0));
-          }
-        CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
-        const size_t np_cnt = (k + 1 < nt ? hp_off[k + 1] : np_off[k]) - np_off[k];
-        const bool timed = profiling && np_cnt > 0;
-        if (timed)
-          CU(cudaEventRecord(pev[2 * k], np));
-        r = update(np, A, ld, map_local, nbox_local, k, buf, np_off[k], np_cnt, true);
-        if (r != 0)
-          return r;
-        if (timed)
-          CU(cudaEventRecord(pev[2 * k + 1], np));
-        np_timed[k] = timed;
-        CU(cudaEventRecord(ev_np[buf], np));
+        else {
+          if (up_on && k == up_steps)
+            for (int g = 0; g < kUpGroups; ++g) {  // join: from here on one launch per step again
+              CU(cudaStreamWaitEvent(np, ev_grp[0][g], 0));
+              CU(cudaStreamWaitEvent(np, ev_grp[1][g], 0));
+              CU(cudaStreamWaitEvent(np, ev_up[g], 0));
+            }
+          CU(cudaStreamWaitEvent(np, ev_panel[buf], 0));
+          const size_t np_cnt = (k + 1 < nt ? hp_off[k + 1] : np_off[k]) - np_off[k];
+          const bool timed = profiling && np_cnt > 0;
+          if (timed)
+            CU(cudaEventRecord(pev[2 * k], np));
+          r = update(np, A, ld, map_local, nbox_local, k, buf, np_off[k], np_cnt, true);
+          if (r != 0)
+            return r;
+          if (timed)
+            CU(cudaEventRecord(pev[2 * k + 1], np));
+          np_timed[k] = timed;
+          CU(cudaEventRecord(ev_np[buf], np));
+        }
+        if (pp.on && split)
+          for (int g = 0; g < kUpGroups; ++g)  // "step consumed" below is raised on np: after the group launches
+            CU(cudaStreamWaitEvent(np, ev_grp[buf][g], 0));
       }
       if (pp.on) {
         // "step k consumed here": after the look-ahead update, the bulk update and my forwarding copies of this step

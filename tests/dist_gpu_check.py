@@ -141,6 +141,18 @@ def main():
                         ncases += 1
                         if fail:
                             failures.append(msg)
+                # host pointers through dlaf_pdpotrf with >= 16 tile columns: the upload of the local block is
+                # overlapped with the first steps (column groups on their own stream, split bulk updates)
+                for n, nb in ([(4608, 128)] if QUICK else [(2304, 128), (4608, 128), (2200, 64)]):
+                    a = orc.gen_hpd(n, nb, np.float64)
+                    ref = a.copy(order="F")
+                    assert orc.cholesky_local("L", ref, nb) == 0
+                    tol = 50 * n * np.finfo(np.float64).eps * np.sqrt(2.0)
+                    fail, msg = run_case("d", "L", n, nb, a, ref, tol,
+                                         f"random host-pointer d L n={n} nb={nb} grid={P}x{Q}", True)
+                    ncases += 1
+                    if fail:
+                        failures.append(msg)
             L.dlaf_free_grid(ctx)
             grid.close()
 
