@@ -80,7 +80,7 @@ def test_miniapp_cholesky_grid_overload_single_rank():
     exe = os.path.join(ROOT, "dla-future_b200", "bin", "miniapp_cholesky")
     if not os.path.exists(exe):
         pytest.skip("miniapp not built (make miniapp)")
-    cmd = [exe, "--matrix-size", "1536", "--block-size", "512", "--type", "d", "--check-result", "all", "--nruns", "1",
+    cmd = [exe, "--matrix-size", "1536", "--block-size", "512", "--type", "d", "--check-result", "all", "--nruns", "1", "--nwarmups", "0",
            "--csv"]
     r = subprocess.run(cmd, capture_output=True, text=True, env=_env(), timeout=600)
     assert r.returncode == 0, (r.stdout + r.stderr)[-3000:]
