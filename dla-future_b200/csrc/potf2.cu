@@ -19,6 +19,8 @@
 // profiles/r01/latency_b200.txt). This version: 75 us; the 512 x 512 tile built from it: 1170 -> 362 us.
 #include "tile_ops.cuh"
 
+#include <cstdlib>
+
 namespace dlafb {
 namespace {
 
@@ -49,7 +51,7 @@ struct Potf2Smem {
 // in the l loop, and the read-modify-write adds a selected zero instead of branching per element.
 template <class T, int BS, int NMAX, int CBN>
 __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __restrict__ Xp, int n, int r0, int bs,
-                                               bool factor, bool inv, int tx, int col0) {
+                                               bool factor, bool inv, int tx, int col0, int cend) {
   constexpr int RA = NMAX / 32;
   constexpr int LDS = Potf2Smem<T, NMAX>::lds;
   T acc[RA][CBN];
@@ -80,7 +82,7 @@ __device__ __forceinline__ void potf2_trailing(T* __restrict__ S, const T* __res
 #pragma unroll
   for (int ib = 0; ib < CBN; ++ib) {
     const int col = col0 + 16 * ib;
-    const bool colok = col < n;
+    const bool colok = col < cend;  // cend <= n: the columns this update is limited to
     T* dcol = S + (colok ? col : NMAX) * LDS;
 #pragma unroll
     for (int ia = 0; ia < RA; ++ia) {
@@ -222,13 +224,13 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
       const int nib = col0 < n ? (n - col0 + 15) >> 4 : 0;
       constexpr int CB = (NMAX - BS + 15) / 16;
       if (CB > 6 && nib > 6)
-        potf2_trailing<T, BS, NMAX, (CB > 6 ? 8 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, (CB > 6 ? 8 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0, n);
       else if (CB > 4 && nib > 4)
-        potf2_trailing<T, BS, NMAX, (CB > 4 ? 6 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, (CB > 4 ? 6 : CB)>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0, n);
       else if (nib > 2)
-        potf2_trailing<T, BS, NMAX, 4>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, 4>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0, n);
       else if (nib > 0)
-        potf2_trailing<T, BS, NMAX, 2>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0);
+        potf2_trailing<T, BS, NMAX, 2>(S, Xp, n, r0, bs, FACTOR, inv, tx, col0, n);
     }
     __syncthreads();
     STAMP(6 + 3 * (jb / BS));
@@ -262,7 +264,32 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
   STAMP(62);
 }
 
+#include "potf2_d128.cuh"
+
 }  // namespace
+
+// factor + inverse of a full 128 x 128 lower double block: the delayed-update kernel (DLAFB_POTF2_FAST=0: the generic one)
+template <class T>
+bool launch_potf2_fast(cudaStream_t, int, int, T*, long long, T*, long long, int*, int, int) {
+  return false;
+}
+template <>
+bool launch_potf2_fast<double>(cudaStream_t stream, int upper, int n, double* a, long long lda, double* w,
+                               long long ldw, int* info, int info_base, int mode) {
+  static const bool on = [] {
+    const char* e = getenv("DLAFB_POTF2_FAST");
+    return !(e && e[0] == '0');
+  }();
+  if (!on || upper || n != kP128 || mode != 3 || w == nullptr)
+    return false;
+  static cudaError_t attr =
+      cudaFuncSetAttribute(potf2_d128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kP128Smem);
+  if (attr != cudaSuccess)
+    return false;
+  potf2_d128_kernel<<<1, kPotf2Threads, kP128Smem, stream>>>(a, lda, w, ldw, info, info_base);
+  ++g_launches;
+  return true;
+}
 
 template <class T>
 cudaError_t launch_potf2(cudaStream_t stream, char uplo, int n, T* a, long long lda, T* winv, long long ldw,
@@ -282,6 +309,8 @@ cudaError_t launch_potf2(cudaStream_t stream, char uplo, int n, T* a, long long 
     return attr_f != cudaSuccess ? attr_f : attr_i;
   T* w = (mode & 2) ? winv : nullptr;
   const int up = uplo == 'U' || uplo == 'u';
+  if (launch_potf2_fast<T>(stream, up, n, a, lda, w, ldw, info, info_base, mode))
+    return cudaGetLastError();
   if (mode & 1)
     kern_f<<<1, kPotf2Threads, smem, stream>>>(up, n, a, lda, w, ldw, info, info_base);
   else if (w != nullptr)
