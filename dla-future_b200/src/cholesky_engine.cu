@@ -387,7 +387,11 @@ struct Plan final : dlafb_chol_plan {
     std::vector<Info> all((size_t)W);
     uint8_t* xbuf = nullptr;
     CU(cudaMalloc(&xbuf, sizeof(Info) * (size_t)(W + 1)));
-    CU(cudaMemcpy(xbuf, &mine, sizeof(Info), cudaMemcpyHostToDevice));
+    // (the plain cudaMemcpy / cudaMemset calls of this file are ordered on the legacy stream only, and a host-to-device
+    // copy from pageable memory may still be in flight when it returns: nothing on the plan's non-blocking streams is
+    // ordered after them until the cudaDeviceSynchronize at the end of init())
+    CU(cudaDeviceSynchronize());  // the memset of the arena above
+    CU(cudaMemcpyAsync(xbuf, &mine, sizeof(Info), cudaMemcpyHostToDevice, g->stream));
     NC(ncclAllGather(xbuf, xbuf + sizeof(Info), sizeof(Info), ncclUint8, g->world, g->stream));
     CU(cudaStreamSynchronize(g->stream));
     CU(cudaMemcpy(all.data(), xbuf + sizeof(Info), sizeof(Info) * (size_t)W, cudaMemcpyDeviceToHost));
@@ -418,7 +422,7 @@ struct Plan final : dlafb_chol_plan {
     }
     // second agreement: every rank opened every handle it needs
     int* flag = reinterpret_cast<int*>(xbuf);
-    CU(cudaMemcpy(flag, &ok, sizeof(int), cudaMemcpyHostToDevice));
+    CU(cudaMemcpyAsync(flag, &ok, sizeof(int), cudaMemcpyHostToDevice, g->stream));
     NC(ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, g->world, g->stream));
     CU(cudaStreamSynchronize(g->stream));
     CU(cudaMemcpy(&ok, flag, sizeof(int), cudaMemcpyDeviceToHost));
@@ -623,6 +627,11 @@ struct Plan final : dlafb_chol_plan {
       ldt = round_up(mloc > 0 ? mloc : 1, 64);
       CU(cudaMalloc(&tbuf, ((size_t)ldt * (nloc > 0 ? nloc : 1) + 64) * sizeof(T)));
     }
+    // The uploads and memsets above went through the legacy stream; the plan works on non-blocking streams, which are
+    // not ordered after it, and a cudaMemcpy from pageable host memory may return before its DMA has finished. Without
+    // this a run right after plan creation could read update lists that had not arrived yet (seen as an
+    // order-dependent failure of the redistribution lists, which had the same pattern: profiles/r02/flaky_upload.md).
+    CU(cudaDeviceSynchronize());
     return 0;
   }
 
@@ -833,6 +842,7 @@ struct Plan final : dlafb_chol_plan {
           map_pc_s[0] = map_pr_s[0];
         }
       }
+      CU(cudaDeviceSynchronize());  // legacy-stream uploads / memsets above vs the non-blocking hp stream below
       r_ready = true;
     }
     const ncclDataType_t nt_ = NcclType<T>::t;

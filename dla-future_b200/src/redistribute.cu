@@ -106,6 +106,12 @@ int prepare(RedistPlan& p, long long ld_src, long long ld_dst, cudaStream_t s) {
       return (int)e;
     p.recv_cap = rb;
   }
+  // The lists were uploaded with cudaMemcpy from pageable memory: it is ordered on the legacy stream only and may return
+  // before its DMA has finished, while the copy kernel runs on the caller's (possibly non-blocking) stream. Without
+  // this the kernel could read a list that had not arrived: rectangles of 0 x 0 elements, nothing copied
+  // (order-dependent failure of dlaf_p?potrf with DLAFB_POTRF_REDISTRIBUTE=1, profiles/r02/flaky_upload.md).
+  if ((e = cudaDeviceSynchronize()) != cudaSuccess)
+    return (int)e;
   p.ld_src = ld_src;
   p.ld_dst = ld_dst;
   return 0;
