@@ -38,6 +38,7 @@ TILE_API = {
 PLAIN_API = {
     "dlafb_inner_block": (c_int, [c_char, c_vp, c_i64, c_int]),
     "dlafb_potrf_work_elems": (c_sz, [c_char, c_int, c_int]),
+    "dlafb_potrf_tile_noalloc_d": (c_int, [c_vp, c_char, c_int, c_vp, c_i64, c_vp, c_int]),
 }
 
 

@@ -36,6 +36,17 @@ int dlafb_inner_block(char type, const void* a, int64_t lda, int nb);
 /* Workspace, in ELEMENTS, that dlafb_potrf_tile_X needs for an n x n tile. */
 size_t dlafb_potrf_work_elems(char type, int n, int ib);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate
+ * device memory (code under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * dlafb_potrf_tile_d with its workspace in a file-scope device array of the library (2.5 MiB held by every GPU that
+ * loads the library until the process exits) instead of a caller-supplied buffer: in-place Cholesky of the uplo
+ * triangle of the n x n double tile a, info as above. n <= DLAFB_POTRF_NOALLOC_MAX_N, larger n is rejected
+ * (cudaErrorInvalidValue = 1 and a message on stderr). Calls no cudaMalloc / cudaFree / allocating routine. Every
+ * call shares the array (the part used is cleared first, on `stream`): calls whose work overlaps on the GPU race -
+ * keep them ordered (one stream, or events between streams). */
+#define DLAFB_POTRF_NOALLOC_MAX_N 512
+int dlafb_potrf_tile_noalloc_d(void* stream, char uplo, int n, double* a, int64_t lda, int* info_dev, int info_base);
+
 #define DLAFB_DECLARE_TILE_API(X, T)                                                                               \
   /* In-place Cholesky of the uplo ('L'/'U') triangle of the n x n tile a. On return work[j*ib*ib ..] (ld = ib)   \
    * holds inv(L_jj) for the j-th ib x ib diagonal block (L = U^H for uplo 'U'). */                                \
