@@ -318,6 +318,11 @@ def independent_residual(a0, lfac, ld, rows, cols, n, nb, P, Q, pr, pc, world, c
     assert len(ridx[pr]) == rows and len(cidx[pc]) == cols
     A = torch.as_strided(a0, (rows, cols), (1, ld))
     Lm = torch.as_strided(lfac, (rows, cols), (1, ld))
+    # single precision: the checker works in double, so that its own rounding (sqrt(n) eps32 in a float matmul) does not
+    # hide the factorization's
+    wide = {torch.float32: torch.float64, torch.complex64: torch.complex128}.get(a0.dtype)
+    if wide is not None:
+        A = A.to(wide)
 
     def tri_max(M):  # max |M_ij| over global row >= global column, in column chunks (bounded temporaries)
         v = 0.0
@@ -343,12 +348,12 @@ def independent_residual(a0, lfac, ld, rows, cols, n, nb, P, Q, pr, pc, world, c
         piece[:rows, :mine.shape[1]] = mine
         allp = torch.empty(world, rmax, wmax, dtype=a0.dtype, device=dev)
         dist.all_gather_into_tensor(allp.view(-1), piece.view(-1))
-        Lk = torch.zeros(n, w, dtype=a0.dtype, device=dev)
+        Lk = torch.zeros(n, w, dtype=A.dtype, device=dev)
         for r in range(world):
             rp, rq = r // Q, r % Q       # row-major grid (bench.py creates the grid with ordering 'R')
             cs = cidx[rq][(cidx[rq] >= c_lo) & (cidx[rq] < c_hi)] - c_lo
             if len(cs) and len(ridx[rp]):
-                Lk[ridx[rp][:, None], cs[None, :]] = allp[r, :len(ridx[rp]), :len(cs)]
+                Lk[ridx[rp][:, None], cs[None, :]] = allp[r, :len(ridx[rp]), :len(cs)].to(Lk.dtype)
         Lk.tril_(-c_lo)                  # the factor is lower triangular: global row >= global column
         # rows / columns of this rank at or below the block column's first row
         r0 = int(torch.searchsorted(ridx[pr], c_lo).item())
@@ -377,7 +382,7 @@ def main():
     ap.add_argument("--config", default="headline", choices=["headline", "zpotrf", "float", "weak"],
                     help="BASELINE.json configuration: headline (configs[1] / [2]), zpotrf (configs[3]), float / weak (configs[4])")
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed dist_parity leg (N > 1)")
-    ap.add_argument("--n", type=int, default=None)
+    ap.add_argument("--n", "--size", dest="n", type=int, default=None)
     ap.add_argument("--nb", type=int, default=None)
     ap.add_argument("--cpu-n", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")

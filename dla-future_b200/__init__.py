@@ -26,6 +26,7 @@ c_sz = ctypes.c_size_t
 TILE_API = {
     "dlafb_potrf_tile_{x}": (c_int, [c_vp, c_char, c_int, c_vp, c_i64, c_vp, c_int, c_vp, c_int]),
     "dlafb_trsm_panel_{x}": (c_int, [c_vp, c_int, c_vp, c_i64, c_vp, c_int, c_vp, c_i64, c_int]),
+    "dlafb_trsm_panel_packed_{x}": (c_int, [c_vp, c_int, c_vp, c_i64, c_vp, c_int, c_vp, c_i64, c_int, c_vp, c_int]),
     "dlafb_gemm_nt_{x}": (c_int, [c_vp, c_int, c_int, c_int, c_dbl, c_vp, c_i64, c_vp, c_i64, c_dbl, c_vp, c_i64,
                                   c_int]),
     "dlafb_transpose_{x}": (c_int, [c_vp, c_int, c_int, c_vp, c_i64, c_vp, c_i64, c_int, c_char]),

@@ -42,6 +42,11 @@ size_t dlafb_potrf_work_elems(char, int n, int ib) { return potrf_work_elems<dou
                            int m) {                                                                                \
     return (int)trsm_panel<T>(st(s), nk, (const T*)l, ldl, (const T*)w, ib, (T*)b, ldb, m);                       \
   }                                                                                                                \
+  int dlafb_trsm_panel_packed_##X(void* s, int nk, const CT* l, int64_t ldl, const CT* w, int ib, CT* b,          \
+                                  int64_t ldb, int m, CT* packed, int tile) {                                      \
+    return (int)trsm_panel_packed<T>(st(s), nk, (const T*)l, ldl, (const T*)w, ib, (T*)b, ldb, m, (T*)packed,     \
+                                     tile);                                                                        \
+  }                                                                                                                \
   int dlafb_gemm_nt_##X(void* s, int m, int n, int k, double alpha, const CT* a, int64_t lda, const CT* b,        \
                         int64_t ldb, double beta, CT* c, int64_t ldc, int lower) {                                 \
     return (int)gemm_nt<T>(st(s), m, n, k, (Tr<T>::Real)alpha, (const T*)a, lda, (const T*)b, ldb,                \

@@ -34,8 +34,56 @@ constexpr int kP128 = 128;           // block order handled by the kernel below
 constexpr int kP128Lds = kP128 + 9;  // S: odd column stride (as Potf2Smem)
 constexpr int kP128Xld = kP128 + 8;  // XS row stride: the 4 k-rows x 8 rows of a fragment load hit distinct bank pairs
 constexpr int kP128Sp = 32;          // super-panel width
+constexpr int kP128Pld = kP128 + 4;  // Xp row stride: k * 132 + row hits 16 distinct bank pairs per half-warp
 constexpr size_t kP128Smem =
-    ((size_t)kP128Lds * (kP128 + 1) + (size_t)8 * kP128 + (size_t)kP128Sp * kP128Xld + kP128) * sizeof(double) + 16;
+    ((size_t)kP128Lds * (kP128 + 1) + (size_t)8 * kP128Pld + (size_t)kP128Sp * kP128Xld + kP128) * sizeof(double) + 16;
+
+// S(:, 8 cb0 .. 8 fb_end) -= X X^T on the FP64 tensor pipe, X = the K columns just factored ([k][row], row stride XLD):
+// E rows (fragment rows fa < cb0) take every column, L rows only the fragments on or below the diagonal. Warp w owns the
+// 8-row fragment fa = w: its A operand is loaded once and reused for all its column fragments, four of which are in
+// flight at a time (the first version did one fragment at a time: 8 dependent DMMAs, 1.3 k cycles per fragment).
+template <int K, int XLD>
+__device__ __forceinline__ void p128_dmma_update(double* __restrict__ S, const double* __restrict__ X, int cb0,
+                                                 int fb_end, int warp, int lane) {
+  constexpr int LDS = kP128Lds;
+  const int r = lane >> 2, kk = lane & 3;
+  const int fa = warp;
+  const int fb_hi = fa < cb0 ? fb_end : min(fb_end, fa + 1);  // exclusive
+  if (cb0 >= fb_hi)
+    return;  // warp-uniform
+  double xa[K / 4];
+#pragma unroll
+  for (int i = 0; i < K / 4; ++i)
+    xa[i] = -X[(4 * i + kk) * XLD + 8 * fa + r];
+  for (int fb0 = cb0; fb0 < fb_hi; fb0 += 4) {
+    double acc[4][2];
+    double* cp[4];
+    const double* xb[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int fb = min(fb0 + u, fb_hi - 1);  // beyond the end: recompute the last fragment, do not store it
+      cp[u] = S + (8 * fa + r) + (8 * fb + 2 * kk) * LDS;
+      xb[u] = X + kk * XLD + 8 * fb + r;
+      acc[u][0] = cp[u][0];
+      acc[u][1] = cp[u][LDS];
+    }
+#pragma unroll
+    for (int i = 0; i < K / 4; ++i)
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        dmma884_acc(acc[u][0], acc[u][1], xa[i], xb[u][4 * i * XLD]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int fb = fb0 + u;
+      // the diagonal fragment of the L part keeps its strict upper triangle (E values live there)
+      const bool diag = fa == fb;
+      if (fb < fb_hi && (!diag || r >= 2 * kk))
+        cp[u][0] = acc[u][0];
+      if (fb < fb_hi && (!diag || r >= 2 * kk + 1))
+        cp[u][LDS] = acc[u][1];
+    }
+  }
+}
 
 // One 8-column panel (columns jb .. jb+7) for this thread's row: see the generic kernel for the roles.
 // Leaves the finished panel row in x[], the inverse pivots in dinv, the first failing column (1-based) in fail.
@@ -100,7 +148,7 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
   extern __shared__ __align__(16) unsigned char smraw[];
   double* S = reinterpret_cast<double*>(smraw);   // lower: A -> L; strict upper: E = inv(L)^H
   double* Xp = S + (size_t)LDS * (N + 1);          // current panel, BS x N (rows < r0 from E, rows >= r0 from L)
-  double* XS = Xp + BS * N;                        // super-panel operand, SP x XLD
+  double* XS = Xp + BS * kP128Pld;                 // super-panel operand, SP x XLD
   double* dinv = XS + SP * XLD;                    // 1 / L_jj
   int* sfail = reinterpret_cast<int*>(dinv + N);
 
@@ -141,7 +189,7 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
           if (ps)
             Sp[row + c * LDS] = x[c];
           if (roleA ? row >= r0 : row < r0)
-            Xp[c * N + row] = x[c];
+            Xp[c * kP128Pld + row] = x[c];
           if (roleA) {
             if (row >= r0)
               XS[(l0 + c) * XLD + row] = (row >= c0 + SP) ? x[c] : 0.0;  // rows of E that have not started: zero
@@ -155,10 +203,8 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
       if (fail)
         break;  // uniform
       STAMP(5 + 3 * (jb / BS));
-      if (r0 < c0 + SP) {  // rank-8 update of the rest of the super-panel: warp w owns columns r0 + w, r0 + w + 16
-        const int col0 = r0 + warp;
-        if (col0 < c0 + SP)
-          potf2_trailing<double, BS, N, 2>(S, Xp, N, r0, BS, true, true, lane, col0, c0 + SP);
+      if (r0 < c0 + SP) {  // rank-8 update of the rest of the super-panel
+        p128_dmma_update<BS, kP128Pld>(S, Xp, r0 / 8, (c0 + SP) / 8, warp, lane);
         __syncthreads();
         STAMP(6 + 3 * (jb / BS));
       }
@@ -167,31 +213,8 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
       break;
     const int cb0 = (c0 + SP) / 8;  // first fragment column right of the super-panel
     if (cb0 < N / 8) {
-      // rank-32 update of everything right of the super-panel on the FP64 tensor pipe. Fragment (fa, fb) = rows
-      // 8 fa .., columns 8 fb ..: E rows (fa < cb0) take every column, L rows only on or below the diagonal.
-      const int r = lane >> 2, kk = lane & 3;
-      int item = 0;
-      for (int fb = cb0; fb < N / 8; ++fb) {
-        const int nrow = cb0 + (N / 8 - fb);
-        for (int i = 0; i < nrow; ++i, ++item) {
-          if ((item & 15) != warp)
-            continue;
-          const int fa = i < cb0 ? i : fb + (i - cb0);
-          double* cp = S + (8 * fa + r) + (8 * fb + 2 * kk) * LDS;
-          double acc0 = cp[0], acc1 = cp[LDS];
-          const double* xa = XS + kk * XLD + 8 * fa + r;
-          const double* xb = XS + kk * XLD + 8 * fb + r;
-#pragma unroll
-          for (int l = 0; l < SP; l += 4)
-            dmma884_acc(acc0, acc1, -xa[l * XLD], xb[l * XLD]);
-          // the diagonal fragment of the L part keeps its strict upper triangle (E values live there)
-          const bool diag = fa == fb;
-          if (!diag || r >= 2 * kk)
-            cp[0] = acc0;
-          if (!diag || r >= 2 * kk + 1)
-            cp[LDS] = acc1;
-        }
-      }
+      // rank-32 update of everything right of the super-panel
+      p128_dmma_update<SP, XLD>(S, XS, cb0, N / 8, warp, lane);
       __syncthreads();
       STAMP(6 + 3 * ((c0 + SP) / BS - 1));
     }

@@ -180,6 +180,10 @@ cudaError_t trsm_panel(cudaStream_t stream, int nk, const T* L, long long ldl, c
   if (m <= 0 || nk <= 0)
     return cudaSuccess;
   cudaError_t e;
+  if constexpr (std::is_same<T, double>::value) {
+    if (trsm_panel_fused_d(stream, nk, L, ldl, W, ib, B, ldb, m, nullptr, 0, &e))
+      return e;  // one kernel
+  }
   for (int j0 = 0, j = 0; j0 < nk; j0 += ib, ++j) {
     const int w = nk - j0 < ib ? nk - j0 : ib;
     T* bj = B + (long long)j0 * ldb;
@@ -195,13 +199,30 @@ cudaError_t trsm_panel(cudaStream_t stream, int nk, const T* L, long long ldl, c
   return cudaSuccess;
 }
 
+template <class T>
+cudaError_t trsm_panel_packed(cudaStream_t stream, int nk, const T* L, long long ldl, const T* W, int ib, T* B,
+                              long long ldb, int m, T* packed, int tile) {
+  if (m <= 0 || nk <= 0)
+    return cudaSuccess;
+  cudaError_t e;
+  if constexpr (std::is_same<T, double>::value) {
+    if (trsm_panel_fused_d(stream, nk, L, ldl, W, ib, B, ldb, m, packed, tile, &e))
+      return e;
+  }
+  if ((e = trsm_panel<T>(stream, nk, L, ldl, W, ib, B, ldb, m)) != cudaSuccess)
+    return e;
+  return pack_tiles<T>(stream, m, nk, B, ldb, packed, tile);
+}
+
 #define DLAFB_INST(T)                                                                                              \
   template cudaError_t gemm_nt<T>(cudaStream_t, int, int, int, Tr<T>::Real, const T*, long long, const T*, long long, \
                                   Tr<T>::Real, T*, long long, int);                                                \
   template int inner_block<T>(const T*, long long, int);                                                           \
   template size_t potrf_work_elems<T>(int, int);                                                                   \
   template cudaError_t potrf_tile<T>(cudaStream_t, char, int, T*, long long, T*, int, int*, int);                  \
-  template cudaError_t trsm_panel<T>(cudaStream_t, int, const T*, long long, const T*, int, T*, long long, int);
+  template cudaError_t trsm_panel<T>(cudaStream_t, int, const T*, long long, const T*, int, T*, long long, int);  \
+  template cudaError_t trsm_panel_packed<T>(cudaStream_t, int, const T*, long long, const T*, int, T*, long long,  \
+                                            int, T*, int);
 DLAFB_INST(float)
 DLAFB_INST(double)
 DLAFB_INST(float2)

@@ -50,6 +50,18 @@ template <class T>
 cudaError_t trsm_panel(cudaStream_t stream, int nk, const T* L, long long ldl, const T* W, int ib, T* B,
                        long long ldb, int m);
 
+// The same solve followed by the copy of the solved panel into tile layout (pack_tiles below: row i of B -> slot
+// i / tile of `packed`), which is how the distributed factorization hands the panel to the exchange. One launch on the
+// fused path.
+template <class T>
+cudaError_t trsm_panel_packed(cudaStream_t stream, int nk, const T* L, long long ldl, const T* W, int ib, T* B,
+                              long long ldb, int m, T* packed, int tile);
+
+// One-kernel panel solve for double (csrc/trsm_fused.cu). Returns false when the case is not the fused kernel's; the
+// caller then takes the multi-launch path. `packed` may be null.
+bool trsm_panel_fused_d(cudaStream_t stream, int nk, const double* L, long long ldl, const double* W, int ib, double* B,
+                        long long ldb, int m, double* packed, int tile, cudaError_t* err);
+
 // out (n x m) <- op(in (m x n)), op = transpose (+ conjugate when conj != 0); tri: 'G' all, 'L' / 'U' only that
 // triangle of OUT is written.
 template <class T>

@@ -1038,8 +1038,9 @@ struct Plan final : dlafb_chol_plan {
             const int m_below = (int)(mloc - (int64_t)st.il0 * nb);
             if (m_below > 0) {
               T* B = A + (size_t)st.il0 * nb + (size_t)st.lk_col * nb * ld;
-              CU(trsm_panel<T>(hp, (int)nb, Lkk, ldl, DW, ib, B, ld, m_below));
-              CU(pack_tiles<T>(hp, m_below, (int)nb, B, ld, Pr[buf] + (size_t)st.il0 * slot, (int)nb));
+              // solve + copy into the row panel (tile layout): one kernel for double
+              CU(trsm_panel_packed<T>(hp, (int)nb, Lkk, ldl, DW, ib, B, ld, m_below, Pr[buf] + (size_t)st.il0 * slot,
+                                      (int)nb));
             }
             const int e = sink_column(st, k, A, ld);
             if (e != 0)

@@ -55,6 +55,11 @@ int dlafb_potrf_tile_noalloc_d(void* stream, char uplo, int n, double* a, int64_
   /* B (m x nk) <- B * L^-H, L the nk x nk lower factor, w = the inverted diagonal blocks left by potrf_tile. */   \
   int dlafb_trsm_panel_##X(void* stream, int nk, const T* l, int64_t ldl, const T* w, int ib, T* b, int64_t ldb,  \
                            int m);                                                                                 \
+  /* The same solve, and the solved panel also copied into tile layout: row i of b -> slot i / tile of `packed`        \
+   * (contiguous tile x tile column-major tiles; what the row panel of the distributed factorization holds, reference \
+   * matrix::Panel with tileLayout, include/dlaf/matrix/panel.h:389-391). One kernel for double when nk % 128 == 0. */ \
+  int dlafb_trsm_panel_packed_##X(void* stream, int nk, const T* l, int64_t ldl, const T* w, int ib, T* b,             \
+                                  int64_t ldb, int m, T* packed, int tile);                                           \
   /* C (M x N) <- beta*C + alpha * A (M x K) * B (N x K)^H, real alpha/beta; lower != 0: only i >= j is touched    \
    * and (complex) the diagonal is kept real: with A == B this is herk(Lower, NoTrans). */                         \
   int dlafb_gemm_nt_##X(void* stream, int m, int n, int k, double alpha, const T* a, int64_t lda, const T* b,     \

@@ -26,7 +26,7 @@ import bench  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--n", "--size", dest="n", type=int, default=32768)
     ap.add_argument("--nb", type=int, default=512)
     ap.add_argument("--nrhs", type=int, default=None)
     ap.add_argument("--steps", type=int, default=3)

@@ -32,7 +32,7 @@ EPS = {"s": 2.0 ** -23, "d": 2.0 ** -52, "c": 2.0 ** -23, "z": 2.0 ** -52}
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--type", default="z")
-    ap.add_argument("--n", type=int, default=40960)
+    ap.add_argument("--n", "--size", dest="n", type=int, default=40960)
     ap.add_argument("--nb", type=int, default=512)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--no-check", action="store_true")

@@ -26,7 +26,7 @@ TORCH = {"s": torch.float32, "d": torch.float64, "c": torch.complex64, "z": torc
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=32768)
+    ap.add_argument("--n", "--size", dest="n", type=int, default=32768)
     ap.add_argument("--nb-src", type=int, default=64)
     ap.add_argument("--nb-dst", type=int, default=512)
     ap.add_argument("--type", default="d")

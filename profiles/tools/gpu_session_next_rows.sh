@@ -17,6 +17,11 @@ step() {  # step NAME SECONDS COMMAND...
   local name=$1 secs=$2
   shift 2
   echo "=== $name: $*" | tee -a "$OUT/summary.txt"
+  if [ "$1" = "torchrun_n" ]; then  # `timeout` cannot run a shell function: expand it here
+    local n=$2 port=$3
+    shift 3
+    set -- $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@"
+  fi
   timeout "$secs" "$@" > "$OUT/$name.log" 2>&1
   local rc=$?
   echo "=== $name rc=$rc" | tee -a "$OUT/summary.txt"

@@ -156,7 +156,10 @@ def test_herk_lower(L, x, n, k, extra):
 # -------------------------------------------------------------------------------------------- trsm
 @pytest.mark.parametrize("x", TYPES)
 @pytest.mark.parametrize("m,nk,extra", [(0, 1, 0), (1, 1, 0), (3, 7, 1), (10, 128, 0), (13, 32, 2), (50, 64, 0), (64, 128, 0),
-                                        (300, 128, 0), (1000, 256, 0), (384, 512, 0), (100, 200, 3)])
+                                        (300, 128, 0), (1000, 256, 0), (384, 512, 0), (100, 200, 3),
+                                        # the one-kernel solve (double, nk % 128 == 0): ragged row blocks, several waves,
+                                        # 16- and 32-row CTAs (m > 4736), odd leading dimension of B
+                                        (2501, 512, 0), (4805, 384, 0), (5000, 256, 1), (17, 512, 0), (9700, 512, 0)])
 def test_trsm_panel(L, x, m, nk, extra):
     """B <- B L^-H (Right, Lower, ConjTrans, NonUnit, alpha 1; impl.h:55-67) after potrf of the diagonal tile."""
     dt = NP[x]
@@ -180,6 +183,39 @@ def test_trsm_panel(L, x, m, nk, extra):
     tol = 10 * (m + 1) * orc.type_error(dt)
     assert near(B.get(), ref, tol)
     assert np.all(B.pad() == dt(-7.7))
+
+
+@pytest.mark.parametrize("x", TYPES)
+@pytest.mark.parametrize("m,nk,tile", [(700, 256, 256), (1030, 512, 512), (300, 128, 256), (40, 24, 32), (2600, 512, 512)])
+def test_trsm_panel_packed(L, x, m, nk, tile):
+    """Solve + copy into the row panel's tile layout (one kernel for double): the packed copy must equal the solved B
+    bit for bit, slots beyond the rows stay untouched."""
+    dt = NP[x]
+    rng = np.random.default_rng(m + nk)
+    g = rnd(rng, (nk, nk), dt)
+    akk = g @ g.conj().T + nk * np.eye(nk, dtype=dt)
+    b = rnd(rng, (m, nk), dt)
+    Akk, B = DevMat(akk), DevMat(b, m + 2)
+    ib = min(L.dlafb_inner_block(x.encode(), Akk.ptr, Akk.ld, nk), L.dlafb_inner_block(x.encode(), B.ptr, B.ld, nk))
+    work = DevMat(np.zeros((L.dlafb_potrf_work_elems(x.encode(), nk, ib), 1), dtype=dt))
+    info = DevMat(np.zeros((1, 1), dtype=np.int32))
+    nslots = -(-m // tile)
+    P = DevMat(np.full((tile * tile * nslots, 1), -3.3, dtype=dt))
+    s = stream_ptr()
+    assert getattr(L, f"dlafb_potrf_tile_{x}")(s, b"L", nk, Akk.ptr, Akk.ld, work.ptr, ib, info.ptr, 0) == 0
+    assert getattr(L, f"dlafb_trsm_panel_packed_{x}")(s, nk, Akk.ptr, Akk.ld, work.ptr, ib, B.ptr, B.ld, m, P.ptr,
+                                                      tile) == 0
+    sync()
+    ref = np.asfortranarray(b.copy())
+    orc.tile_trsm_L(np.asfortranarray(np.tril(Akk.get())), ref)
+    got = B.get()
+    assert near(got, ref, 10 * (m + 1) * orc.type_error(dt))
+    assert np.all(B.pad() == dt(-7.7))
+    packed = P.get()[:, 0].reshape(nslots, tile, tile)          # [slot][col][row]
+    for sl in range(nslots):
+        rows = min(tile, m - sl * tile)
+        assert np.array_equal(packed[sl, :nk, :rows].T, got[sl * tile: sl * tile + rows, :])
+        assert np.all(packed[sl, nk:, :] == dt(-3.3)) and np.all(packed[sl, :, rows:] == dt(-3.3))
 
 
 # --------------------------------------------------------------------------------------------- aux
