@@ -17,7 +17,14 @@
 
 #include "../../include/dlafb_engine.h"
 #include "../../include/dlafb_matrix.h"
+// MPI_Comm: with -DDLAFB_WITH_MPI the application's real <mpi.h> (the reference's contract: dlaf_create_grid takes a
+// real communicator, include/dlaf_c/grid.h:31, src/communication/communicator_grid.cpp:36-38); otherwise the
+// single-node shim, whose communicator is {rank, size, NCCL world} set up by dlafb_mpi_init.
+#ifdef DLAFB_WITH_MPI
+#include <mpi.h>
+#else
 #include "../../include/dlafb_mpi_shim/mpi.h"
+#endif
 #include "grid.h"
 
 #include <dlaf_c/factorization/cholesky.h>
@@ -29,15 +36,68 @@ DLAF_EXTERN_C char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow
 DLAF_EXTERN_C void dlaf_create_grid_from_blacs_info(int blacs_ctxt, MPI_Comm comm, int nprow, int npcol,
                                                     char order) DLAF_NOEXCEPT;
 
+#ifndef DLAFB_WITH_MPI
 struct dlafb_mpi_comm {
   int rank = 0, size = 1;
   ncclComm_t world = nullptr;
 };
+#endif
 
 namespace {
 
 bool g_initialized = false;
+#ifndef DLAFB_WITH_MPI
 dlafb_mpi_comm* g_world = nullptr;
+#endif
+
+[[noreturn]] void die(const char* what, int code);
+
+// ---- what the grid code needs from a communicator: rank, size, an NCCL communicator over the same ranks, and a
+//      logical-and over the ranks (grid_ordering) ----
+#ifdef DLAFB_WITH_MPI
+int comm_rank(MPI_Comm c) {
+  int r = 0;
+  if (MPI_Comm_rank(c, &r) != MPI_SUCCESS)
+    die("MPI_Comm_rank failed", -1);
+  return r;
+}
+int comm_size(MPI_Comm c) {
+  int n = 1;
+  if (MPI_Comm_size(c, &n) != MPI_SUCCESS)
+    die("MPI_Comm_size failed", -1);
+  return n;
+}
+// One NCCL communicator per grid over the ranks of `c`: rank 0 creates the id, MPI_Bcast hands it out. The grid owns it.
+ncclComm_t comm_nccl(MPI_Comm c, bool* owned) {
+  ncclUniqueId id;
+  std::memset(&id, 0, sizeof(id));
+  if (comm_rank(c) == 0 && ncclGetUniqueId(&id) != ncclSuccess)
+    die("ncclGetUniqueId failed", -1);
+  if (MPI_Bcast(&id, (int)sizeof(id), MPI_BYTE, 0, c) != MPI_SUCCESS)
+    die("MPI_Bcast of the NCCL id failed", -1);
+  ncclComm_t w = nullptr;
+  const ncclResult_t r = ncclCommInitRank(&w, comm_size(c), id, comm_rank(c));
+  if (r != ncclSuccess)
+    die("ncclCommInitRank failed", 1000 + (int)r);
+  *owned = true;
+  return w;
+}
+void comm_land2(MPI_Comm c, int flags[2]) {
+  int out[2] = {0, 0};
+  if (MPI_Allreduce(flags, out, 2, MPI_INT, MPI_MIN, c) != MPI_SUCCESS)
+    die("MPI_Allreduce failed", -1);
+  flags[0] = out[0];
+  flags[1] = out[1];
+}
+#else
+int comm_rank(MPI_Comm c) { return c ? c->rank : 0; }
+int comm_size(MPI_Comm c) { return c ? c->size : 1; }
+ncclComm_t comm_nccl(MPI_Comm c, bool* owned) {
+  *owned = false;  // the shim's world communicator outlives the grids
+  return c ? c->world : nullptr;
+}
+void comm_land2(MPI_Comm c, int flags[2]);  // below: all-reduce on the shim's NCCL communicator
+#endif
 std::unordered_map<int, dlafb_grid_t> g_grids;
 
 struct PlanKey {
@@ -277,12 +337,26 @@ void pxpotrf(char type, char uplo, int n, void* a, int ia, int ja, const int des
     *info = r;
 }
 
+#ifndef DLAFB_WITH_MPI
+void comm_land2(MPI_Comm c, int flags[2]) {
+  int* dev = nullptr;
+  CAPI_CUDA(cudaMalloc(&dev, 2 * sizeof(int)), "device allocation failed");
+  CAPI_CUDA(cudaMemcpy(dev, flags, 2 * sizeof(int), cudaMemcpyHostToDevice), "upload failed");
+  if (ncclAllReduce(dev, dev, 2, ncclInt, ncclMin, c->world, nullptr) != ncclSuccess)
+    die("grid_ordering: all-reduce failed", -1);
+  CAPI_CUDA(cudaStreamSynchronize(nullptr), "stream synchronisation failed");
+  CAPI_CUDA(cudaMemcpy(flags, dev, 2 * sizeof(int), cudaMemcpyDeviceToHost), "download failed");
+  cudaFree(dev);
+}
+#endif
+
 }  // namespace
 
 extern "C" {
 
 int dlafb_capi_cached_plans(void) { return (int)g_plans.size(); }
 
+#ifndef DLAFB_WITH_MPI
 // ---- MPI shim ----
 MPI_Comm dlafb_mpi_comm_world(void) { return g_world; }
 
@@ -325,6 +399,7 @@ int MPI_Comm_size(MPI_Comm comm, int* size) {
   *size = comm ? comm->size : 1;
   return MPI_SUCCESS;
 }
+#endif  // !DLAFB_WITH_MPI
 
 // ---- init ----
 void dlaf_initialize(int, const char**, int argc_dlaf, const char** argv_dlaf) noexcept {
@@ -357,13 +432,16 @@ void dlaf_finalize(void) noexcept {
 static dlafb_grid_t make_grid(MPI_Comm comm, int nprow, int npcol, char order) {
   dlafb_grid_t g = nullptr;
   int e;
-  const int size = comm ? comm->size : 1;
+  const int size = comm_size(comm);
   if (size != nprow * npcol)
     die("grid size does not match the communicator size", size);
   if (size == 1)
     e = dlafb_grid_create_local(&g);
-  else
-    e = dlafb_grid_create_from_nccl(&g, comm->world, 0, comm->rank, size, nprow, npcol, order);
+  else {
+    bool owned = false;
+    ncclComm_t world = comm_nccl(comm, &owned);
+    e = dlafb_grid_create_from_nccl(&g, world, owned ? 1 : 0, comm_rank(comm), size, nprow, npcol, order);
+  }
   if (e != 0)
     die("grid creation failed", e);
   return g;
@@ -382,6 +460,10 @@ int dlaf_create_grid(MPI_Comm comm, int nprow, int npcol, char order) noexcept {
   int ctx = INT_MAX - (int)g_grids.size();
   while (g_grids.count(ctx))
     --ctx;
+#ifdef DLAFB_WITH_MPI
+  if (MPI_Barrier(comm) != MPI_SUCCESS)  // src/c_api/grid.cpp:35
+    die("MPI_Barrier failed", -1);
+#endif
   g_grids[ctx] = make_grid(comm, nprow, npcol, order);
   return ctx;
 }
@@ -406,18 +488,10 @@ void dlaf_free_grid(int context) noexcept {
 char grid_ordering(MPI_Comm comm, int nprow, int npcol, int myprow, int mypcol) noexcept {
   // src/c_api/grid.cpp:45-70: both tests are all-reduced (logical and) over the communicator, because rank 0 and every
   // rank on the "diagonal" of the two numberings satisfy both; column-major wins when both hold everywhere.
-  const int rank = comm ? comm->rank : 0;
+  const int rank = comm_rank(comm);
   int flags[2] = {rank == myprow * npcol + mypcol ? 1 : 0, rank == mypcol * nprow + myprow ? 1 : 0};
-  if (comm && comm->size > 1) {
-    int* dev = nullptr;
-    CAPI_CUDA(cudaMalloc(&dev, sizeof(flags)), "device allocation failed");
-    CAPI_CUDA(cudaMemcpy(dev, flags, sizeof(flags), cudaMemcpyHostToDevice), "upload failed");
-    if (ncclAllReduce(dev, dev, 2, ncclInt, ncclMin, comm->world, nullptr) != ncclSuccess)
-      die("grid_ordering: all-reduce failed", -1);
-    CAPI_CUDA(cudaStreamSynchronize(nullptr), "stream synchronisation failed");
-    CAPI_CUDA(cudaMemcpy(flags, dev, sizeof(flags), cudaMemcpyDeviceToHost), "download failed");
-    cudaFree(dev);
-  }
+  if (comm_size(comm) > 1)
+    comm_land2(comm, flags);
   if (!flags[0] && !flags[1])
     die("grid_ordering: grid layout must be row major or column major", rank);
   return flags[1] ? 'C' : 'R';

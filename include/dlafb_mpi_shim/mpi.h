@@ -2,9 +2,10 @@
  * It keeps the MPI_Comm-typed signatures of the reference's C and C++ APIs compiling and gives them meaning for
  * the one-process-per-GPU launch this build targets: a communicator is {rank, size, NCCL unique id}; the
  * launcher (torchrun + torch.distributed, or any other) distributes the unique id and calls dlafb_mpi_init.
- * An application that uses a real MPI bootstraps this handle with its own rank / size and an id it broadcasts with
- * MPI_Bcast, from a translation unit that includes this header and not the real <mpi.h> (both define MPI_Comm);
- * passing real MPI communicators into the library is not supported in this build. */
+ * An application that uses a real MPI builds the library with -DDLAFB_WITH_MPI and its own <mpi.h> on the include
+ * path instead of this directory: dlaf_create_grid / grid_ordering / dlaf_create_grid_from_blacs_info then take the real
+ * communicator (rank and size from MPI, the NCCL id over MPI_Bcast, src/c_api.cu). That build is compile-checked
+ * against a stub <mpi.h> only (tests/test_cxx_headers.py): this image has no MPI to run it with. */
 #ifndef DLAFB_MPI_SHIM_H
 #define DLAFB_MPI_SHIM_H
 

@@ -37,3 +37,25 @@ def test_c_headers_are_plain_c_and_every_symbol_links(pkg, tmp_path):
     r = subprocess.run(["gcc", "-std=c99"] + inc + [src, "-o", str(tmp_path / "c_link"), "-L" + libdir, "-ldlaf_b200",
                         "-Wl,-rpath," + libdir, "-Wl,--allow-shlib-undefined"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_real_mpi_bootstrap_compiles(tmp_path):
+    """-DDLAFB_WITH_MPI: dlaf_create_grid(MPI_Comm, ...) takes a REAL communicator as in the reference
+    (include/dlaf_c/grid.h:31): rank / size from MPI, the NCCL id over MPI_Bcast, grid_ordering over MPI_Allreduce. No MPI
+    on this image: src/c_api.cu is compiled (not linked, not run) against tests/cxx/mpi_stub/mpi.h, and the object must
+    reference the MPI functions and no longer define the shim's."""
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("needs nvcc")
+    obj = str(tmp_path / "c_api_mpi.o")
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O1", "-std=c++17", "-DDLAFB_WITH_MPI",
+           "-I" + os.path.join(ROOT, "tests", "cxx", "mpi_stub"), "-I" + os.path.join(ROOT, "include"),
+           "-I" + os.path.join(ROOT, "dla-future_b200", "csrc"), "-I" + os.path.join(ROOT, "dla-future_b200", "src"),
+           "-Xcompiler", "-fPIC,-Wall", "-c", os.path.join(ROOT, "dla-future_b200", "src", "c_api.cu"), "-o", obj]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    syms = subprocess.run(["nm", obj], capture_output=True, text=True).stdout
+    for name in ("MPI_Bcast", "MPI_Allreduce", "MPI_Comm_rank", "MPI_Comm_size", "MPI_Barrier"):
+        assert f" U {name}" in syms, name
+    assert "dlafb_mpi_init" not in syms and " T MPI_Comm_rank" not in syms
+    assert " T dlaf_create_grid" in syms and " T dlaf_pdpotrf" in syms
