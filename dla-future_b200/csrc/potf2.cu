@@ -31,8 +31,12 @@ __device__ long long g_potf2_clk[64];
 #define STAMP(i)          \
   if (threadIdx.x == 0)   \
   g_potf2_clk[i] = clock64()
+#define STAMPT(i, t)       \
+  if (threadIdx.x == (t))  \
+  g_potf2_clk[i] = clock64()
 #else
 #define STAMP(i)
+#define STAMPT(i, t)
 #endif
 
 template <class T, int NMAX>

@@ -103,6 +103,9 @@ __device__ __forceinline__ void p128_panel(const double* __restrict__ Sp, int jb
     const bool keep = roleA ? (act && (t >= BS || c <= t)) : (act && t < 0);
     x[c] = keep ? xv : ((!roleA && act && t == c) ? 1.0 : 0.0);
   }
+  if (jb == 32) {  // fine-grained timing of one panel (DLAFB_TIMING builds only)
+    STAMPT(52, 0);
+  }
   double lraw[BS];
 #pragma unroll
   for (int c = 1; c < BS; ++c)
@@ -138,6 +141,17 @@ __device__ __forceinline__ void p128_panel(const double* __restrict__ Sp, int jb
         lraw[c] = shfl(Dr[j + 1], (tid & 24) + c);  // element (c, j + 1), final after this column's update
     }
     is = is_next;
+    if (jb == 32 && j == 0) {
+      STAMPT(53, 0);
+    }
+    if (jb == 32 && j == 3) {
+      STAMPT(54, 0);
+    }
+  }
+  if (jb == 32) {
+    STAMPT(55, 0);
+    STAMPT(57, 128);  // first E-role warp
+    STAMPT(58, 96);   // last A-role warp
   }
 }
 
@@ -196,6 +210,10 @@ __global__ void __launch_bounds__(kPotf2Threads, 1)
           }
           else if (row < r0)
             XS[(l0 + c) * XLD + row] = x[c];
+        }
+        if (jb == 32) {
+          STAMPT(56, 0);
+          STAMPT(59, 128);
         }
       }
       __syncthreads();

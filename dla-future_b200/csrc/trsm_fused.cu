@@ -14,6 +14,9 @@
 // 16 w .. 16 w + 15 of the block; the 128 x 16 K-slices of the streamed operand are double-buffered with cp.async.
 // R = 16: 116 KB of shared memory and <= 128 registers, so a CTA fits on an SM beside one resident bulk-update CTA
 // (108 KB) instead of waiting for a whole SM; R = 32 for tall panels (half the L2 traffic per row).
+// Measured alone (profiles/r02/chain_probe_*.json): m = 1024: 73.6 -> 54.2 us, m = 4096: 92.5 -> 69.8 us; about 60 % of
+// the DMMA rate per CTA. A 4-stage ring of 8-column slices was slower (68.9 / 86.4 us: twice the barriers, and the
+// loop is bound by the tensor pipe and the barriers, not by the L2 latency of the streamed operand).
 // Bound: latency / L2 (it is on the critical path); algorithmic HBM bytes 8 * nk^2 / 2 + 2 * 8 * m * nk.
 #include <cuda_runtime.h>
 
@@ -224,7 +227,14 @@ bool trsm_panel_fused_d(cudaStream_t stream, int nk, const double* L, long long 
     const char* e = getenv("DLAFB_TRSM_FUSED");
     return e ? atoi(e) : 1;
   }();
-  if (mode == 0 || ib != kTfBlk || nk <= 0 || nk % kTfBlk != 0 || m <= 0)
+  // Tall panels stay on the multi-launch path: a CTA of the fused kernel streams all of L and W for its 16 / 32 rows
+  // (4x / 2x the L2 traffic per row of the 128-row contraction blocks): m = 16384 took 310 us against 222 us, and the
+  // early steps, where panels are tall, hide the solve behind a long bulk update anyway.
+  static const int max_m = [] {
+    const char* e = getenv("DLAFB_TRSM_FUSED_MAX_M");
+    return e ? atoi(e) : 8192;
+  }();
+  if (mode == 0 || ib != kTfBlk || nk <= 0 || nk % kTfBlk != 0 || m <= 0 || m > max_m)
     return false;
   if ((reinterpret_cast<uintptr_t>(L) & 15) || (reinterpret_cast<uintptr_t>(W) & 15) || (ldl & 1))
     return false;  // 16-byte cp.async of the streamed operand

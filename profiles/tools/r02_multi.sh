@@ -31,21 +31,37 @@ export DLAFB_DIST_WORLDS=$N
 if [ "$N" -ge 6 ]; then export DLAFB_DIST_QUICK=1; fi
 step dist_gpu_check 900 trun tests/dist_gpu_check.py
 step bench_headline 900 trun bench.py --gpus "$N" --steps 3 --warmup 3 --timeline "$OUT/timeline"
-if [ "$MODE" != "quick" ]; then
+case "$MODE" in
+full)   # 2 GPUs: everything
   step bench_zpotrf 900 trun bench.py --gpus "$N" --config zpotrf --steps 3 --warmup 2
   step bench_float 900 trun bench.py --gpus "$N" --config float --steps 3 --warmup 2
   step bench_weak 900 trun bench.py --gpus "$N" --config weak --steps 3 --warmup 2
-  if [ "$N" -eq 8 ]; then
-    step bench_weak_ragged 600 trun bench.py --gpus "$N" --config weak --size 92682 --steps 2 --warmup 1 --no-check --no-e2e
-  elif [ "$N" -eq 2 ]; then
-    step bench_weak_ragged 600 trun bench.py --gpus "$N" --config weak --size 46341 --steps 2 --warmup 1 --no-check --no-e2e
-  fi
+  step bench_weak_ragged 600 trun bench.py --gpus "$N" --config weak --size 46341 --steps 2 --warmup 1 --no-check --no-e2e
   step dist_trsolve 900 trun tests/dist_trsolve_check.py
   step dist_g2s 900 trun tests/dist_g2s_check.py
   step dist_redistribute 900 trun tests/dist_redistribute_check.py
   step dist_submatrix 900 trun tests/dist_submatrix_check.py
-  NN=65536; if [ "$N" -le 2 ]; then NN=32768; fi
-  step bench_dist_rows 1200 trun profiles/tools/bench_dist_rows.py --size "$NN" --nb 512
-  step bench_redistribute 300 trun profiles/tools/bench_redistribute.py --size "$NN"
-fi
+  step bench_dist_rows 1200 trun profiles/tools/bench_dist_rows.py --size 32768 --nb 512
+  step bench_redistribute 300 trun profiles/tools/bench_redistribute.py --size 32768
+  ;;
+n4)     # 2 x 2: parity of the distributed rows + their timings + the weak-scaling point
+  step dist_trsolve 900 trun tests/dist_trsolve_check.py
+  step dist_g2s 900 trun tests/dist_g2s_check.py
+  step dist_redistribute 900 trun tests/dist_redistribute_check.py
+  step dist_submatrix 900 trun tests/dist_submatrix_check.py
+  step bench_weak 900 trun bench.py --gpus "$N" --config weak --steps 2 --warmup 2
+  step bench_dist_rows 1200 trun profiles/tools/bench_dist_rows.py --size 65536 --nb 512
+  ;;
+n8)     # 2 x 4: the BASELINE configurations, the panel-solve variants, the distributed rows' timings
+  step bench_zpotrf 900 trun bench.py --gpus "$N" --config zpotrf --steps 3 --warmup 2
+  step bench_float 900 trun bench.py --gpus "$N" --config float --steps 3 --warmup 2
+  step bench_weak 900 trun bench.py --gpus "$N" --config weak --steps 2 --warmup 2
+  step bench_nofused 600 env DLAFB_TRSM_FUSED=0 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" \
+      --master-addr 127.0.0.1 --master-port 29790 bench.py --gpus "$N" --steps 3 --warmup 2 --no-e2e --no-check --timeline "$OUT/timeline_nofused"
+  step bench_fused_all 600 env DLAFB_TRSM_FUSED_MAX_M=100000 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" \
+      --master-addr 127.0.0.1 --master-port 29791 bench.py --gpus "$N" --steps 3 --warmup 2 --no-e2e --no-check --timeline "$OUT/timeline_fusedall"
+  step bench_weak_ragged 600 trun bench.py --gpus "$N" --config weak --size 92682 --steps 2 --warmup 1 --no-check --no-e2e
+  step bench_dist_rows 1200 trun profiles/tools/bench_dist_rows.py --size 65536 --nb 512
+  ;;
+esac
 echo "=== done" | tee -a "$OUT/summary.txt"
