@@ -58,7 +58,7 @@ n8)     # 2 x 4: the BASELINE configurations, the panel-solve variants, the dist
   step bench_weak 900 trun bench.py --gpus "$N" --config weak --steps 2 --warmup 2
   step bench_nofused 600 env DLAFB_TRSM_FUSED=0 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" \
       --master-addr 127.0.0.1 --master-port 29790 bench.py --gpus "$N" --steps 3 --warmup 2 --no-e2e --no-check --timeline "$OUT/timeline_nofused"
-  step bench_fused_all 600 env DLAFB_TRSM_FUSED_MAX_M=100000 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" \
+  step bench_fused_all 600 env DLAFB_TRSM_FUSED=16 DLAFB_TRSM_FUSED_MAX_M=100000 $PY -m torch.distributed.run --nnodes=1 --nproc-per-node "$N" \
       --master-addr 127.0.0.1 --master-port 29791 bench.py --gpus "$N" --steps 3 --warmup 2 --no-e2e --no-check --timeline "$OUT/timeline_fusedall"
   step bench_weak_ragged 600 trun bench.py --gpus "$N" --config weak --size 92682 --steps 2 --warmup 1 --no-check --no-e2e
   step bench_dist_rows 1200 trun profiles/tools/bench_dist_rows.py --size 65536 --nb 512
