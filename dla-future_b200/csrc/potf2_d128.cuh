@@ -15,7 +15,8 @@
 // Same augmented-matrix formulation as the generic kernel: E = inv(L)^H grows in the strict upper triangle of S,
 // W = E^H. Row r of XS holds, for the big update, L(r, c0 + l) when r >= c0 + 32 and E(r, c0 + l) when r < c0 + 32
 // (zero where row r of E has not started yet).
-// Measured (profiles/r02/potf2_d128_timing.json): 75.3 -> 65.2 us for the block, 358.7 -> 323.0 us for the 512 tile.
+// Measured (profiles/r02/potf2_d128_timing.json): 75.3 -> 65.2 us for the block with the scalar rank-8 update and one
+// DMMA fragment at a time, 58.0 us with both updates on p128_dmma_update; the 512 tile 358.7 -> 292 - 304 us.
 __device__ __forceinline__ double rsqrt_nobranch(double d) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));

@@ -227,12 +227,15 @@ bool trsm_panel_fused_d(cudaStream_t stream, int nk, const double* L, long long 
     const char* e = getenv("DLAFB_TRSM_FUSED");
     return e ? atoi(e) : 1;
   }();
-  // Tall panels stay on the multi-launch path: a CTA of the fused kernel streams all of L and W for its 16 / 32 rows
-  // (4x / 2x the L2 traffic per row of the 128-row contraction blocks): m = 16384 took 310 us against 222 us, and the
-  // early steps, where panels are tall, hide the solve behind a long bulk update anyway.
+  // Tall panels stay on the multi-launch path: a CTA of the fused kernel streams all of L and W for its rows (4x the L2
+  // traffic per row of the 128-row contraction blocks; alone m = 16384 takes 310 us against 222 us), and the early
+  // steps, where panels are tall, hide the solve behind a long bulk update anyway. Measured with 16-row CTAs:
+  // no limit: 1 GPU n = 32768 348.0 ms (345.1 without), 8 GPUs n = 65536 384.7 ms (389.1 with the first default, limit
+  // 8192 and 32-row CTAs above 4736 rows; 387.6 ms on the multi-launch path); limit 20480: 1 GPU 346.0 ms
+  // (profiles/r02/session3_summary.txt, profiles/r02/n8/). DLAFB_TRSM_FUSED_MAX_M overrides.
   static const int max_m = [] {
     const char* e = getenv("DLAFB_TRSM_FUSED_MAX_M");
-    return e ? atoi(e) : 8192;
+    return e ? atoi(e) : 20480;
   }();
   if (mode == 0 || ib != kTfBlk || nk <= 0 || nk % kTfBlk != 0 || m <= 0 || m > max_m)
     return false;
@@ -246,7 +249,9 @@ bool trsm_panel_fused_d(cudaStream_t stream, int nk, const double* L, long long 
   const bool fits16 = trsm_fused_smem<16>(nk) <= 227 * 1024, fits32 = trsm_fused_smem<32>(nk) <= 227 * 1024;
   if (!fits16)
     return false;
-  const bool tall = mode == 32 || (mode != 16 && m > 16 * 2 * gemm_sm_count());
+  // 16-row CTAs by default: a CTA fits beside a resident bulk-update CTA and starts as soon as one retires (in situ on
+  // 8 GPUs the solve took 0.36 ms instead of 0.76 ms at k = 60); DLAFB_TRSM_FUSED=32 selects 32-row CTAs
+  const bool tall = mode == 32;
   *err = (tall && fits32) ? launch_trsm_fused<32>(stream, p) : launch_trsm_fused<16>(stream, p);
   return true;
 }
