@@ -32,8 +32,14 @@ __device__ __forceinline__ void dmma884_acc(double& c0, double& c1, double a, do
 }
 
 constexpr int kP128 = 128;           // block order handled by the kernel below
-constexpr int kP128Lds = kP128 + 9;  // S: odd column stride (as Potf2Smem)
-constexpr int kP128Xld = kP128 + 8;  // XS row stride: the 4 k-rows x 8 rows of a fragment load hit distinct bank pairs
+// Strides chosen for the DMMA fragment accesses (lane = 4 r + kk; a half-warp is r = 0..3, kk = 0..3; 16 bank pairs of
+// 8 bytes): operands X[(4 i + kk) * XLD + 8 f + r] need kk * XLD + r distinct mod 16 -> XLD = 4 mod 16; accumulators
+// S[(8 fa + r) + (8 fb + 2 kk + e) * LDS] need 2 kk * LDS + r distinct mod 16 -> LDS = 2 mod 4. (ncu of the first
+// version, LDS = 137 and XLD = 136: 13.4 k bank conflicts in 50 k shared-memory wavefronts,
+// profiles/r02/ncu_potf2_d128.json.) Row walks (lanes along a column) are conflict-free for any stride; only the final
+// read of E along rows pays a 2-way conflict (1 k wavefronts, once).
+constexpr int kP128Lds = kP128 + 2;
+constexpr int kP128Xld = kP128 + 4;
 constexpr int kP128Sp = 32;          // super-panel width
 constexpr int kP128Pld = kP128 + 4;  // Xp row stride: k * 132 + row hits 16 distinct bank pairs per half-warp
 constexpr size_t kP128Smem =

@@ -158,7 +158,10 @@ void evict_lru_plans(const PlanKey& keep) {
   }
 }
 
+void drop_redist_of(int ctx);
+
 void drop_plans_of(int ctx) {
+  drop_redist_of(ctx);
   for (auto it = g_plans.begin(); it != g_plans.end();) {
     if (ctx == INT_MIN || it->first.ctx == ctx) {
       destroy_entry(it->second);
@@ -193,8 +196,43 @@ int redistribution_block(int n, int nb_in) {
       die(what, (int)ce_);               \
   } while (0)
 
-int cholesky_redistributed(dlafb_grid_t grid, char type, char uplo, void* a, int n, int nb_in, int isrc, int jsrc,
-                           int64_t ld, int nb_to) {
+// What the redistributed path keeps between calls (round 2: creating the three plans, two device blocks and a stream on
+// every call cost ~85 ms at n = 16384, more than the factorization): at most two entries, least recently used first out,
+// dropped with their grid.
+struct RedistEntry {
+  dlafb_redistribute_plan_t fwd = nullptr, bwd = nullptr;
+  dlafb_chol_plan_t plan = nullptr;
+  cudaStream_t stream = nullptr;
+  void* in_dev = nullptr;   // device image of the caller's block (host-pointer callers)
+  void* work = nullptr;     // the block at the factorization's block size
+  size_t in_bytes = 0, work_bytes = 0;
+  unsigned long long last_use = 0;
+};
+std::map<PlanKey, RedistEntry> g_redist;
+
+void destroy_redist(RedistEntry& r) {
+  dlafb_redistribute_plan_destroy(r.fwd);
+  dlafb_redistribute_plan_destroy(r.bwd);
+  dlafb_cholesky_plan_destroy(r.plan);
+  cudaFree(r.in_dev);
+  cudaFree(r.work);
+  if (r.stream)
+    cudaStreamDestroy(r.stream);
+}
+
+void drop_redist_of(int ctx) {
+  for (auto it = g_redist.begin(); it != g_redist.end();) {
+    if (ctx == INT_MIN || it->first.ctx == ctx) {
+      destroy_redist(it->second);
+      it = g_redist.erase(it);
+    }
+    else
+      ++it;
+  }
+}
+
+int cholesky_redistributed(int ctx, dlafb_grid_t grid, char type, char uplo, void* a, int n, int nb_in, int isrc,
+                           int jsrc, int64_t ld, int nb_to) {
   const size_t es = elem_size(type);
   const int64_t rows_in = dlafb_dist_local_size(n, nb_in, grid->P, grid->pr, isrc);
   const int64_t cols_in = dlafb_dist_local_size(n, nb_in, grid->Q, grid->pc, jsrc);
@@ -202,8 +240,28 @@ int cholesky_redistributed(dlafb_grid_t grid, char type, char uplo, void* a, int
   const int64_t cols_w = dlafb_dist_local_size(n, nb_to, grid->Q, grid->pc, 0);
   if (rows_in > 0 && ld < rows_in)
     die("leading dimension smaller than the local number of rows", (int)ld);
-  cudaStream_t s;
-  CAPI_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "stream creation failed");
+  const PlanKey key{ctx, type, uplo, n, nb_in, isrc, jsrc};
+  RedistEntry& r = g_redist[key];
+  r.last_use = ++g_plan_clock;
+  int e;
+  if (!r.plan) {
+    while (g_redist.size() > 2) {  // every rank makes the same calls: the same entries go
+      auto victim = g_redist.end();
+      for (auto it = g_redist.begin(); it != g_redist.end(); ++it)
+        if (&it->second != &r && (victim == g_redist.end() || it->second.last_use < victim->second.last_use))
+          victim = it;
+      if (victim == g_redist.end())
+        break;
+      destroy_redist(victim->second);
+      g_redist.erase(victim);
+    }
+    CAPI_CUDA(cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking), "stream creation failed");
+    if ((e = dlafb_redistribute_plan_create(&r.fwd, grid, type, n, n, nb_in, nb_in, isrc, jsrc, nb_to, nb_to, 0, 0)) != 0 ||
+        (e = dlafb_redistribute_plan_create(&r.bwd, grid, type, n, n, nb_to, nb_to, 0, 0, nb_in, nb_in, isrc, jsrc)) != 0 ||
+        (e = dlafb_cholesky_plan_create(&r.plan, grid, type, uplo, n, nb_to, 0, 0)) != 0)
+      die("plan creation failed", e);
+  }
+  cudaStream_t s = r.stream;
   cudaPointerAttributes attr{};
   const bool on_device = (a != nullptr) && cudaPointerGetAttributes(&attr, a) == cudaSuccess &&
                          (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
@@ -213,41 +271,38 @@ int cholesky_redistributed(dlafb_grid_t grid, char type, char uplo, void* a, int
   const bool have_block = rows_in > 0 && cols_in > 0;
   if (!on_device) {
     ld_in = ((rows_in > 0 ? rows_in : 1) + 63) / 64 * 64;
-    CAPI_CUDA(cudaMalloc(&in_dev, (size_t)ld_in * (size_t)(cols_in > 0 ? cols_in : 1) * es), "device allocation failed");
+    const size_t need = (size_t)ld_in * (size_t)(cols_in > 0 ? cols_in : 1) * es;
+    if (r.in_bytes < need) {
+      cudaFree(r.in_dev);
+      CAPI_CUDA(cudaMalloc(&r.in_dev, need), "device allocation failed");
+      r.in_bytes = need;
+    }
+    in_dev = r.in_dev;
     if (have_block)
       CAPI_CUDA(cudaMemcpy2DAsync(in_dev, ld_in * es, a, ld * es, rows_in * es, cols_in, cudaMemcpyHostToDevice, s),
                 "upload failed");
   }
   const int64_t ldw = ((rows_w > 0 ? rows_w : 1) + 63) / 64 * 64;
-  void* work = nullptr;
-  CAPI_CUDA(cudaMalloc(&work, (size_t)ldw * (size_t)(cols_w > 0 ? cols_w : 1) * es), "device allocation failed");
-  dlafb_redistribute_plan_t fwd = nullptr, bwd = nullptr;
-  dlafb_chol_plan_t plan = nullptr;
-  int e;
-  if ((e = dlafb_redistribute_plan_create(&fwd, grid, type, n, n, nb_in, nb_in, isrc, jsrc, nb_to, nb_to, 0, 0)) != 0 ||
-      (e = dlafb_redistribute_plan_create(&bwd, grid, type, n, n, nb_to, nb_to, 0, 0, nb_in, nb_in, isrc, jsrc)) != 0 ||
-      (e = dlafb_cholesky_plan_create(&plan, grid, type, uplo, n, nb_to, 0, 0)) != 0)
-    die("plan creation failed", e);
-  if ((e = dlafb_redistribute_plan_run(fwd, in_dev, ld_in, work, ldw, s)) != 0)
+  const size_t wneed = (size_t)ldw * (size_t)(cols_w > 0 ? cols_w : 1) * es;
+  if (r.work_bytes < wneed) {
+    cudaFree(r.work);
+    CAPI_CUDA(cudaMalloc(&r.work, wneed), "device allocation failed");
+    r.work_bytes = wneed;
+  }
+  void* work = r.work;
+  if ((e = dlafb_redistribute_plan_run(r.fwd, in_dev, ld_in, work, ldw, s)) != 0)
     die("redistribution failed", e);
-  if ((e = dlafb_cholesky_plan_run(plan, work, ldw, s)) != 0)
+  if ((e = dlafb_cholesky_plan_run(r.plan, work, ldw, s)) != 0)
     die("factorization failed to launch", e);
   int info = 0;
-  if ((e = dlafb_cholesky_plan_info(plan, &info)) != 0)
+  if ((e = dlafb_cholesky_plan_info(r.plan, &info)) != 0)
     die("factorization failed", e);
-  if ((e = dlafb_redistribute_plan_run(bwd, work, ldw, in_dev, ld_in, s)) != 0)
+  if ((e = dlafb_redistribute_plan_run(r.bwd, work, ldw, in_dev, ld_in, s)) != 0)
     die("redistribution failed", e);
   if (!on_device && have_block)
     CAPI_CUDA(cudaMemcpy2DAsync(a, ld * es, in_dev, ld_in * es, rows_in * es, cols_in, cudaMemcpyDeviceToHost, s),
               "download failed");
   CAPI_CUDA(cudaStreamSynchronize(s), "stream synchronisation failed");
-  dlafb_redistribute_plan_destroy(fwd);
-  dlafb_redistribute_plan_destroy(bwd);
-  dlafb_cholesky_plan_destroy(plan);
-  cudaFree(work);
-  if (!on_device)
-    cudaFree(in_dev);
-  cudaStreamDestroy(s);
   return info;
 }
 
@@ -280,7 +335,7 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   if (key.uplo != 'L' && key.uplo != 'U')
     die("uplo must be 'L' or 'U'", -1);
   if (const int nb_to = redistribution_block(d.n, d.nb))
-    return cholesky_redistributed(grid, type, key.uplo, a, d.n, d.nb, sub_isrc, sub_jsrc, d.ld, nb_to);
+    return cholesky_redistributed(ctx, grid, type, key.uplo, a, d.n, d.nb, sub_isrc, sub_jsrc, d.ld, nb_to);
   PlanEntry& pe = g_plans[key];
   pe.last_use = ++g_plan_clock;
   int e;
@@ -354,7 +409,7 @@ void comm_land2(MPI_Comm c, int flags[2]) {
 
 extern "C" {
 
-int dlafb_capi_cached_plans(void) { return (int)g_plans.size(); }
+int dlafb_capi_cached_plans(void) { return (int)(g_plans.size() + g_redist.size()); }
 
 #ifndef DLAFB_WITH_MPI
 // ---- MPI shim ----

@@ -49,6 +49,7 @@ def main():
     for nb in (64, 128):
         for flag in ("0", "1"):
             print(json.dumps(timed(b"L", nb, flag)), flush=True)
+            print(json.dumps(timed(b"L", nb, flag, device_ptr=True)), flush=True)
     for uplo in (b"L", b"U"):
         print(json.dumps(timed(uplo, 512, "0")), flush=True)
         print(json.dumps(timed(uplo, 512, "0", device_ptr=True)), flush=True)

@@ -127,6 +127,33 @@ def main():
                             ncases += 1
                             if fail:
                                 failures.append(msg)
+            # ScaLAPACK convention for a matrix that is not positive definite: EVERY rank returns the 1-based global column
+            # of the first non-positive pivot, although only the owner of that diagonal tile sees it
+            for capi in (False, True):
+                n, nb = 6 * 32 + 5, 32
+                a = orc.gen_hpd(n, nb, np.float64)
+                bad_col = 5 * 32 + 3          # in the last full tile: owned by one rank of the grid
+                a[bad_col, bad_col] = -1.0
+                rows = local_index(L, n, nb, P, grid.pr, src[0])
+                cols = local_index(L, n, nb, Q, grid.pc, src[1])
+                ld = max(1, len(rows))
+                host = np.zeros((max(1, len(cols)), ld))
+                host[:len(cols), :len(rows)] = a[np.ix_(rows, cols)].T
+                if capi:
+                    desca = pkg.DESC9(1, ctx, n, n, nb, nb, src[0], src[1], ld)
+                    info = ctypes.c_int(-1)
+                    L.dlaf_pdpotrf(b"L", n, host.ctypes.data, 1, 1, desca, ctypes.byref(info))
+                    inf = info.value
+                else:
+                    plan = pkg.CholeskyPlan(L, grid, "d", "L", n, nb, src)
+                    dev = torch.from_numpy(host.reshape(-1).copy()).cuda()
+                    plan.run(dev.data_ptr(), ld, stream)
+                    inf = plan.info()
+                    torch.cuda.synchronize()
+                    plan.close()
+                ncases += 1
+                if inf != bad_col + 1:
+                    failures.append(f"not-HPD info={inf} (want {bad_col + 1}) grid={P}x{Q}{order} capi={capi}")
             if order == "R":
                 big = [("d", 4096, 128), ("d", 1100, 128)] if QUICK else [("d", 2048, 128), ("d", 1664, 256), ("d", 1100, 128), ("z", 640, 64), ("s", 768, 128)]
                 for x, n, nb in big:
