@@ -175,13 +175,21 @@ void drop_plans_of(int ctx) {
 size_t elem_size(char t) { return t == 's' ? 4 : (t == 'z' ? 16 : 8); }
 
 // Callers that come from ScaLAPACK bring block sizes of 32 - 128; the factorization wants 512 (the contraction's K and
-// the number of dependent steps). With DLAFB_POTRF_REDISTRIBUTE=1 a matrix with a small block size is redistributed on
-// the device to the largest block size <= 512 that is a multiple of both the caller's block size and 16, factorized
-// there and redistributed back (matrix::copy(src, dst, grid), include/dlaf/matrix/copy.h:118-231 of the reference, is
-// the same tool; the reference's C API does not use it for this call). Off by default until it has been timed.
-int redistribution_block(int n, int nb_in) {
+// the number of dependent steps). Such a matrix can be redistributed on the device to the largest block size <= 512
+// that is a multiple of both the caller's block size and 16, factorized there and redistributed back
+// (matrix::copy(src, dst, grid), include/dlaf/matrix/copy.h:118-231 of the reference, is the same tool; the reference's
+// C API does not use it for this call). Measured at n = 16384 on one GPU (profiles/r02/small_blocks.txt):
+//   device pointers  nb = 64: 125.8 ms plain, 49.4 ms redistributed;  nb = 128: 49.8 / 49.5 ms
+//   host pointers    nb = 64: 136.4 / 125.6 ms;  nb = 128: 63.5 / 125.7 ms  (the whole block crosses PCIe both ways,
+//                    unoverlapped, where the plain path moves the triangle only and overlaps it with the factorization)
+// so: DLAFB_POTRF_REDISTRIBUTE unset -> device pointers with nb < 128 only; = 1 -> every call with nb < 256; = 0 -> never.
+int redistribution_block(int n, int nb_in, bool on_device) {
   const char* e = getenv("DLAFB_POTRF_REDISTRIBUTE");
-  if (!e || e[0] != '1' || nb_in >= 256 || n < 2048)
+  const bool forced = e && e[0] == '1';
+  const bool never = e && e[0] == '0';
+  if (never || n < 2048 || nb_in >= 256)
+    return 0;
+  if (!forced && !(on_device && nb_in < 128))
     return 0;
   int l = nb_in;
   while (l % 16 != 0)
@@ -334,7 +342,14 @@ int cholesky(int ctx, char type, char uplo, void* a, const DLAF_descriptor& d) {
   const PlanKey key{ctx, type, uplo == 'u' ? 'U' : (uplo == 'l' ? 'L' : uplo), d.n, d.nb, sub_isrc, sub_jsrc};
   if (key.uplo != 'L' && key.uplo != 'U')
     die("uplo must be 'L' or 'U'", -1);
-  if (const int nb_to = redistribution_block(d.n, d.nb))
+  bool dev_ptr = false;
+  {
+    cudaPointerAttributes pa{};
+    dev_ptr = (a != nullptr) && cudaPointerGetAttributes(&pa, a) == cudaSuccess &&
+              (pa.type == cudaMemoryTypeDevice || pa.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+  }
+  if (const int nb_to = redistribution_block(d.n, d.nb, dev_ptr))
     return cholesky_redistributed(ctx, grid, type, key.uplo, a, d.n, d.nb, sub_isrc, sub_jsrc, d.ld, nb_to);
   PlanEntry& pe = g_plans[key];
   pe.last_use = ++g_plan_clock;

@@ -24,9 +24,10 @@ struct TuneParameters {
   /// DLAFB_SGEMM_WIDE [process]: float contractions on the 128x128 kernel (default since it was timed: 38 vs 27 TFLOP/s
   /// for the n = 32768 factorization); 0 selects the 64x64 kernel.
   int sgemm_wide = env_int("DLAFB_SGEMM_WIDE", 1);
-  /// DLAFB_POTRF_REDISTRIBUTE: dlaf_p?potrf redistributes matrices with block sizes below 256 to <= 512, factorizes and
-  /// redistributes back. Read at every call.
-  int potrf_redistribute = env_int("DLAFB_POTRF_REDISTRIBUTE", 0);
+  /// DLAFB_POTRF_REDISTRIBUTE: dlaf_p?potrf redistributes matrices with small block sizes to <= 512, factorizes and
+  /// redistributes back. -1 (unset): device pointers with nb < 128 only; 1: every call with nb < 256; 0: never. Read at
+  /// every call.
+  int potrf_redistribute = env_int("DLAFB_POTRF_REDISTRIBUTE", -1);
 
   /// Exports the fields to the environment variables the library reads.
   void apply() const {

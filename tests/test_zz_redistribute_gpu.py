@@ -90,3 +90,42 @@ def test_pxpotrf_with_redistribution_to_large_blocks(pkg, L, monkeypatch, x, n, 
     finally:
         L.dlaf_free_grid(ctx)
         L.dlaf_finalize()
+
+
+@pytest.mark.parametrize("uplo", "LU")
+def test_pdpotrf_device_pointer_small_blocks_redistributes_by_default(pkg, L, monkeypatch, uplo):
+    """Without DLAFB_POTRF_REDISTRIBUTE in the environment a DEVICE-pointer caller with nb < 128 (n >= 2048) goes
+    through redistribute -> Cholesky at 512 -> redistribute back (2.5x faster at nb = 64, profiles/r02/small_blocks.txt):
+    same result as the oracle, nothing outside the referenced triangle touched, and the C API keeps the entry cached."""
+    import ctypes
+
+    import dlaf_oracle as orc
+    from gpu_util import DevMat, sync
+    monkeypatch.delenv("DLAFB_POTRF_REDISTRIBUTE", raising=False)
+    ctx = 48
+    L.dlaf_initialize(0, None, 0, None)
+    pkg.check(L.dlafb_mpi_init(0, 1, None), "mpi_init")
+    L.dlaf_create_grid_from_blacs_info(ctx, L.dlafb_mpi_comm_world(), 1, 1, b"R")
+    try:
+        n, nb = 2304, 64
+        a = orc.gen_hpd(n, nb, np.float64)
+        ref = a.copy(order="F")
+        assert orc.cholesky_local(uplo, ref, nb) == 0
+        keep = (np.tril if uplo == "L" else np.triu)(np.ones((n, n))) > 0
+        a_in = np.where(keep, a, -9.9)
+        tol = 50 * n * float(np.finfo(np.float64).eps) * np.sqrt(2.0)
+        before = L.dlafb_capi_cached_plans()
+        for rep in range(2):   # the second call reuses the cached plans and buffers
+            A = DevMat(a_in, ld=n + 8)
+            desca = pkg.DESC9(1, ctx, n, n, nb, nb, 0, 0, A.ld)
+            info = ctypes.c_int(-1)
+            L.dlaf_pdpotrf(uplo.encode(), n, A.ptr, 1, 1, desca, ctypes.byref(info))
+            sync()
+            assert info.value == 0
+            got = A.get()
+            assert np.abs(got[keep] - ref[keep]).max() <= tol * max(1.0, np.abs(ref[keep]).max())
+            assert np.all(got[~keep] == -9.9) and np.all(A.pad() == -7.7)
+            assert L.dlafb_capi_cached_plans() == before + 1
+    finally:
+        L.dlaf_free_grid(ctx)
+        L.dlaf_finalize()
