@@ -29,6 +29,13 @@ struct RedistDesc {
   int mb_d, nb_d, src_r_d, src_c_d;  // destination
   int P, Q, pr, pc;
   char ordering;  // 'R' / 'C': linear rank of (pr, pc) in the full communicator
+  // Round 2: the m x n matrix may be a SUB-MATRIX of a larger distributed matrix on either side: it starts at global
+  // element (off_r, off_c) of a parent with the tile size and source rank above, and the local pointer is the base of
+  // the parent's local block (ScaLAPACK's sub(A) = A(ia : ia + m, ja : ja + n) with any ia, ja; the reference's
+  // SubDistributionSpec, include/dlaf/matrix/distribution.h:60-63). With an offset the tile boundaries of the two sides
+  // need not nest, so the pieces that travel are the intersections of the two tilings.
+  long long off_r_s = 0, off_c_s = 0, off_r_d = 0, off_c_d = 0;
+  bool has_offset() const { return off_r_s != 0 || off_c_s != 0 || off_r_d != 0 || off_c_d != 0; }
 };
 
 struct RedistLists {
@@ -44,6 +51,10 @@ struct RedistLists {
 inline bool redist_valid(const RedistDesc& d) {
   if (d.m < 0 || d.n < 0 || d.mb_s < 1 || d.nb_s < 1 || d.mb_d < 1 || d.nb_d < 1 || d.P < 1 || d.Q < 1)
     return false;
+  if (d.off_r_s < 0 || d.off_c_s < 0 || d.off_r_d < 0 || d.off_c_d < 0)
+    return false;
+  if (d.has_offset())
+    return true;  // sub-matrices: any pair of tilings (the pieces are their intersections)
   const int mb = d.mb_s < d.mb_d ? d.mb_s : d.mb_d, nb = d.nb_s < d.nb_d ? d.nb_s : d.nb_d;
   return d.mb_s % mb == 0 && d.mb_d % mb == 0 && d.nb_s % nb == 0 && d.nb_d % nb == 0;  // copy.h:124-131
 }
@@ -52,27 +63,50 @@ inline int redist_linear_rank(const RedistDesc& d, int pr, int pc) {
   return d.ordering == 'C' ? pc * d.P + pr : pr * d.Q + pc;
 }
 
-// One axis: for every sub-tile i (of size sb) the owner and local element offset in a distribution with tiles of tb.
+// One axis: the pieces [first, first + size) of 0 .. n between consecutive tile boundaries of EITHER side, each with its
+// owner and local element offset on the source side and on the destination side. Without offsets and with nesting
+// tile sizes these are the sub-tiles of the smaller tile size (copy.h:133-216).
 struct RedistAxis {
-  std::vector<int> owner;
-  std::vector<long long> local_off;
   std::vector<int> size;
+  std::vector<int> owner_s, owner_d;
+  std::vector<long long> loff_s, loff_d;
 };
 
-inline RedistAxis redist_axis(long long n, int sb, int tb, int nprocs, int src) {
+inline RedistAxis redist_axis(long long n, int tb_s, long long off_s, int src_s, int tb_d, long long off_d, int src_d,
+                              int nprocs) {
   RedistAxis a;
-  const long long ns = n > 0 ? (n + sb - 1) / sb : 0;
-  a.owner.resize(ns);
-  a.local_off.resize(ns);
-  a.size.resize(ns);
-  for (long long i = 0; i < ns; ++i) {
-    const long long first = i * sb;
-    const long long tile = first / tb;
-    a.owner[i] = (int)((tile + src) % nprocs);
-    a.local_off[i] = (tile / nprocs) * tb + (first - tile * tb);
-    a.size[i] = (int)(n - first < sb ? n - first : sb);
+  for (long long first = 0; first < n;) {
+    const long long gs = off_s + first, gd = off_d + first;  // positions in the two parents
+    const long long to_s = tb_s - gs % tb_s, to_d = tb_d - gd % tb_d;  // distance to the next tile boundary
+    long long size = to_s < to_d ? to_s : to_d;
+    if (size > n - first)
+      size = n - first;
+    const long long ts = gs / tb_s, td = gd / tb_d;
+    a.size.push_back((int)size);
+    a.owner_s.push_back((int)((ts + src_s) % nprocs));
+    a.loff_s.push_back((ts / nprocs) * tb_s + gs % tb_s);
+    a.owner_d.push_back((int)((td + src_d) % nprocs));
+    a.loff_d.push_back((td / nprocs) * tb_d + gd % tb_d);
+    first += size;
   }
   return a;
+}
+
+// Local element range [lo, hi) of one side of an axis on rank `rank` (hi = 0: nothing local). Contiguous: the local
+// elements between the first and the last one of the (sub-)matrix all belong to it.
+inline void redist_local_range(const std::vector<int>& owner, const std::vector<long long>& loff,
+                               const std::vector<int>& size, int rank, long long* lo, long long* hi) {
+  *lo = 0;
+  *hi = 0;
+  bool any = false;
+  for (size_t i = 0; i < owner.size(); ++i)
+    if (owner[i] == rank) {
+      if (!any || loff[i] < *lo)
+        *lo = loff[i];
+      if (!any || loff[i] + size[i] > *hi)
+        *hi = loff[i] + size[i];
+      any = true;
+    }
 }
 
 // ld_src / ld_dst: leading dimensions of the caller's local blocks.
@@ -83,16 +117,17 @@ inline RedistLists redist_build(const RedistDesc& d, long long ld_src, long long
   L.send_cnt.assign(world, 0);
   L.recv_off.assign(world, 0);
   L.recv_cnt.assign(world, 0);
-  L.ls_rows = Dist1D{d.m, d.mb_s, d.P, d.pr, d.src_r_s}.local_size();
-  L.ls_cols = Dist1D{d.n, d.nb_s, d.Q, d.pc, d.src_c_s}.local_size();
-  L.ld_rows = Dist1D{d.m, d.mb_d, d.P, d.pr, d.src_r_d}.local_size();
-  L.ld_cols = Dist1D{d.n, d.nb_d, d.Q, d.pc, d.src_c_d}.local_size();
+  const RedistAxis ra = redist_axis(d.m, d.mb_s, d.off_r_s, d.src_r_s, d.mb_d, d.off_r_d, d.src_r_d, d.P);
+  const RedistAxis ca = redist_axis(d.n, d.nb_s, d.off_c_s, d.src_c_s, d.nb_d, d.off_c_d, d.src_c_d, d.Q);
+  // local extents the caller's blocks must cover (without offsets: the local sizes)
+  long long lo;
+  redist_local_range(ra.owner_s, ra.loff_s, ra.size, d.pr, &lo, &L.ls_rows);
+  redist_local_range(ca.owner_s, ca.loff_s, ca.size, d.pc, &lo, &L.ls_cols);
+  redist_local_range(ra.owner_d, ra.loff_d, ra.size, d.pr, &lo, &L.ld_rows);
+  redist_local_range(ca.owner_d, ca.loff_d, ca.size, d.pc, &lo, &L.ld_cols);
   if (d.m <= 0 || d.n <= 0)
     return L;
-  const int mb = d.mb_s < d.mb_d ? d.mb_s : d.mb_d, nb = d.nb_s < d.nb_d ? d.nb_s : d.nb_d;
-  const RedistAxis rs = redist_axis(d.m, mb, d.mb_s, d.P, d.src_r_s), rd = redist_axis(d.m, mb, d.mb_d, d.P, d.src_r_d);
-  const RedistAxis cs = redist_axis(d.n, nb, d.nb_s, d.Q, d.src_c_s), cd = redist_axis(d.n, nb, d.nb_d, d.Q, d.src_c_d);
-  const long long nI = (long long)rs.owner.size(), nJ = (long long)cs.owner.size();
+  const long long nI = (long long)ra.size.size(), nJ = (long long)ca.size.size();
   // counts first (segment offsets), then the rectangles, both in global column-major order of the sub-tiles
   for (int pass = 0; pass < 2; ++pass) {
     std::vector<long long> send_pos(world, 0), recv_pos(world, 0);
@@ -108,25 +143,25 @@ inline RedistLists redist_build(const RedistDesc& d, long long ld_src, long long
       L.recv_total = r;
     }
     for (long long J = 0; J < nJ; ++J) {
-      const bool col_src_mine = cs.owner[J] == d.pc, col_dst_mine = cd.owner[J] == d.pc;
+      const bool col_src_mine = ca.owner_s[J] == d.pc, col_dst_mine = ca.owner_d[J] == d.pc;
       if (!col_src_mine && !col_dst_mine)
         continue;
       for (long long I = 0; I < nI; ++I) {
-        const bool src_mine = col_src_mine && rs.owner[I] == d.pr;
-        const bool dst_mine = col_dst_mine && rd.owner[I] == d.pr;
+        const bool src_mine = col_src_mine && ra.owner_s[I] == d.pr;
+        const bool dst_mine = col_dst_mine && ra.owner_d[I] == d.pr;
         if (!src_mine && !dst_mine)
           continue;
-        const int rows = rs.size[I], cols = cs.size[J];
+        const int rows = ra.size[I], cols = ca.size[J];
         const long long elems = (long long)rows * cols;
-        const long long soff = rs.local_off[I] + cs.local_off[J] * ld_src;
-        const long long doff = rd.local_off[I] + cd.local_off[J] * ld_dst;
+        const long long soff = ra.loff_s[I] + ca.loff_s[J] * ld_src;
+        const long long doff = ra.loff_d[I] + ca.loff_d[J] * ld_dst;
         if (src_mine && dst_mine) {
           if (pass == 1)
             L.self.push_back(CopyRect{soff, doff, ld_src, ld_dst, rows, cols});
           continue;
         }
         if (src_mine) {
-          const int to = redist_linear_rank(d, rd.owner[I], cd.owner[J]);
+          const int to = redist_linear_rank(d, ra.owner_d[I], ca.owner_d[J]);
           if (pass == 0)
             L.send_cnt[to] += elems;
           else {
@@ -135,7 +170,7 @@ inline RedistLists redist_build(const RedistDesc& d, long long ld_src, long long
           }
         }
         if (dst_mine) {
-          const int from = redist_linear_rank(d, rs.owner[I], cs.owner[J]);
+          const int from = redist_linear_rank(d, ra.owner_s[I], ca.owner_s[J]);
           if (pass == 0)
             L.recv_cnt[from] += elems;
           else {
